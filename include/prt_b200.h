@@ -1,0 +1,236 @@
+/*
+ * prt_b200.h — C ABI of the B200-native path-tracing backend for Pooraytracer.
+ *
+ * The reference (Zoz4/Pooraytracer) has no plugin / FFI boundary: its render path sits behind two
+ * C++ seams that `main.cpp` calls directly,
+ *
+ *     void Camera::Render(Hittable& world, Hittable& lights)         Source/Camera.h:27  (main.cpp:49)
+ *     bool Hittable::Hit(const Ray&, Interval, HitRecord&) const     Source/Hittable.h:34
+ *     void Hittable::Sample(const point3&, HitRecord&, double&)      Source/Hittable.h:36
+ *
+ * This header is the boundary a maintainer would bind instead (INTEGRATION.md shows the stub):
+ * plain pointers and sizes, no C++ / torch types, every call returns an int status (0 = ok) and
+ * never throws. Inputs are copied at create time (the caller keeps ownership); outputs are
+ * caller-allocated. One context is bound to one GPU and is used from one host thread at a time
+ * (one process per GPU; multi-GPU = one context per rank, see prt_render_device).
+ *
+ * There is NO CPU fallback: every compute entry point fails with PRT_ERR_NO_DEVICE when the
+ * context has no usable sm_100 device.
+ *
+ * Conventions
+ *   - all geometry / radiance arithmetic is IEEE binary64, evaluated in the reference's operation
+ *     order without FMA contraction (Source/Triangle.cpp:54-83, Source/AABB.cpp:38-64);
+ *   - prim id  = index of the triangle in prt_scene_desc (the creation order of
+ *     Source/Model.cpp:115-190: shape-major, face-minor);
+ *   - images are row-major, top row first, 3 doubles (linear RGB) per pixel — the layout of
+ *     `Camera::colorAttachment` (Source/Camera.h:26, Source/Camera.cpp:56).
+ */
+#ifndef PRT_B200_H
+#define PRT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PRT_ABI_VERSION 1
+
+/* ---- status codes ---------------------------------------------------------------------------- */
+#define PRT_OK 0
+#define PRT_ERR_INVALID_ARGUMENT (-1)
+#define PRT_ERR_NO_DEVICE (-2)      /* no CUDA device / not an sm_100 part / context has none   */
+#define PRT_ERR_CUDA (-3)           /* a CUDA runtime call failed; see prt_last_error           */
+#define PRT_ERR_OUT_OF_MEMORY (-4)
+#define PRT_ERR_NOT_COMMITTED (-5)  /* compute call on a scene that was not committed           */
+#define PRT_ERR_UNSUPPORTED (-6)
+
+typedef struct prt_context prt_context;
+typedef struct prt_scene prt_scene;
+
+/* ---- materials: numeric values follow `enum class MaterialType` Source/Material.h:48-51 ------ */
+enum prt_material_type {
+    PRT_MAT_LAMBERTIAN = 0,    /* Source/Material.h:101-155 */
+    PRT_MAT_PHONG = 1,         /* PhoneReflectance, Source/Material.h:172-330 */
+    PRT_MAT_MIRROR = 2,        /* PerfectMirror, Source/Material.h:332-366 */
+    PRT_MAT_COOK_TORRANCE = 3, /* Source/Material.h:368-521 */
+    PRT_MAT_DIFFUSE_LIGHT = 4, /* Source/Material.h:157-170 */
+    PRT_MAT_DEBUG = 5,         /* Source/Material.h:523-535 (emits its albedo) */
+    PRT_MAT_EMPTY = 6          /* Source/Material.h:537-540 */
+};
+
+typedef struct prt_material {
+    int32_t type;       /* prt_material_type */
+    int32_t kd_tex;     /* index into prt_scene_desc.textures for map_Kd, or -1 (SolidColor)    */
+    double kd[3];       /* Lambertian albedo / Phong Kd / CookTorrance Kd / Debug albedo        */
+    double ks[3];       /* Phong Ks (ignored when kd_tex >= 0: the reference aliases Ks to the  */
+                        /* Kd texture, Source/Material.h:178-181)                               */
+    double ns;          /* Phong shininess                                                      */
+    double emission[3]; /* DiffuseLight radiance (<light radiance=...>, Source/Model.cpp:332)   */
+    double alpha_x, alpha_y; /* CookTorrance roughness                                          */
+    double eta[3], k[3];     /* CookTorrance complex IOR                                        */
+} prt_material;
+
+/* Decoded image, rows top to bottom, `channels` interleaved u8 per texel — what stbi_load(.., 0)
+ * returns in Source/Texture.cpp:12. texels == NULL reproduces a failed load (cyan,
+ * Source/Texture.cpp:24). */
+typedef struct prt_texture {
+    int32_t width, height, channels, reserved;
+    const uint8_t* texels;
+} prt_texture;
+
+/* Flat scene: what Model::meshes holds after Source/Model.cpp:53-193. */
+typedef struct prt_scene_desc {
+    int64_t n_triangles;
+    const double* vertices;  /* [n_triangles][3][3]  v0,v1,v2 xyz                               */
+    const double* normals;   /* [n_triangles][3][3]  vertex normals (fallback only,             */
+                             /*                      Source/Triangle.cpp:21-29) or NULL = zeros */
+    const double* texcoords; /* [n_triangles][3][2]  or NULL = (0,0),(1,0),(1,1) per triangle   */
+                             /*                      (the degenerate-UV rule Source/Model.cpp:170) */
+    int32_t n_meshes;        /* one per OBJ shape, in file order (main.cpp:37 iteration order)  */
+    const int64_t* mesh_first;     /* [n_meshes+1] triangles of mesh m = [first[m], first[m+1]) */
+    const int32_t* mesh_material;  /* [n_meshes]   material of face 0 rules (Model.cpp:118)     */
+    int32_t n_materials;
+    const prt_material* materials;
+    int32_t n_textures;
+    const prt_texture* textures;
+} prt_scene_desc;
+
+/* ---- acceleration structure ------------------------------------------------------------------ */
+enum prt_accel {
+    /* The reference's own two-level median-split BVH (Source/BVH.cpp:7-48, main.cpp:36-45),
+     * flattened, FP64 boxes, traversed in the reference's order (left then right,
+     * Source/BVH.cpp:51-61) including its duplicated span-1 children. Bit-exact by construction. */
+    PRT_ACCEL_REFERENCE_BVH2 = 0,
+    /* SAH BVH collapsed to 8-wide nodes with outward-rounded FP32 child boxes, near-to-far
+     * ordered traversal, ties resolved by reference DFS rank (last visited wins,
+     * Source/Interval.h:21-23 + Source/BVH.cpp:58). Same hits, far fewer node visits. */
+    PRT_ACCEL_WIDE_BVH8 = 1
+};
+
+typedef struct prt_build_opts {
+    int32_t accel;        /* prt_accel */
+    int32_t reserved[7];
+} prt_build_opts;
+
+/* ---- camera + integrator parameters (public fields of Source/Camera.h:14-33) ------------------ */
+typedef struct prt_camera {
+    int32_t image_width, image_height;
+    double fovy;
+    double eye[3], look_at[3], up[3];
+} prt_camera;
+
+#define PRT_RENDER_EXACT_VISIBILITY 1u /* NEE visibility by closest-hit + the literal distance test
+                                          of Source/Camera.cpp:150-155 instead of any-hit over
+                                          [1e-3, dist-1e-3] (equivalent up to rounding)          */
+#define PRT_RENDER_COUNTERS 2u         /* count BVH node / triangle visits (prt_get_stats)       */
+
+typedef struct prt_render_params {
+    int32_t samples_per_pixel; /* total spp: pixelSamplesScale = 1/spp (Source/Camera.cpp:83)    */
+    int32_t max_depth;         /* Camera::maxDepth: at most max_depth+1 path vertices            */
+    int32_t sample_lights;     /* Camera::bSampleLights                                          */
+    int32_t spp_begin, spp_end;/* this call renders sample indices [spp_begin, spp_end) of every */
+                               /* pixel (spp sharding across GPUs / steps); 0,0 = all            */
+    uint32_t flags;
+    double russian_roulette;   /* Camera::russianRoulette                                        */
+    double background[3];      /* Camera::background                                             */
+    uint64_t rng_key;          /* key of the counter-based generator (pixel, sample, dimension)  */
+} prt_render_params;
+
+typedef struct prt_stats {
+    uint64_t extend_rays;      /* closest-hit rays traced by the last render / trace call        */
+    uint64_t shadow_rays;      /* shadow rays traced                                             */
+    uint64_t paths;            /* camera paths started                                           */
+    uint64_t node_visits;      /* BVH nodes fetched   (only with PRT_RENDER_COUNTERS / counters) */
+    uint64_t tri_tests;        /* triangle records fetched                                       */
+    uint64_t kernel_launches;  /* kernels launched by the last call                              */
+    double   gpu_ms;           /* device time of the last call (CUDA events on its stream)       */
+    double   extend_ms;        /* device time inside the extend kernel(s)                        */
+    double   shade_ms;
+    double   shadow_ms;
+    int32_t  node_bytes;       /* bytes per BVH node of the committed layout                     */
+    int32_t  tri_bytes;        /* bytes per triangle intersection record (128)                   */
+    int64_t  n_nodes;
+    int64_t  n_triangles;
+} prt_stats;
+
+/* ---- lifecycle -------------------------------------------------------------------------------- */
+int prt_abi_version(void);
+
+/* device < 0: host-only context (scene building / flattening only; compute calls fail with
+ * PRT_ERR_NO_DEVICE). Otherwise binds CUDA device `device`. */
+int prt_context_create(int device, prt_context** out);
+void prt_context_destroy(prt_context* ctx);
+/* Message of the last failure on this thread (never NULL). */
+const char* prt_last_error(void);
+
+/* Copies every input; builds the reference-order BVH (needed for the tie rule and for light
+ * sampling whatever accel is chosen later). Replaces: Model::meshes → per-mesh BVHNode →
+ * world / lights HittableList construction, main.cpp:33-45. */
+int prt_scene_create(prt_context* ctx, const prt_scene_desc* desc, prt_scene** out);
+/* Flattens into the chosen layout and uploads to HBM. */
+int prt_scene_commit(prt_scene* scene, const prt_build_opts* opts);
+void prt_scene_destroy(prt_scene* scene);
+
+/* Host-side introspection (no GPU needed): the reference DFS order the tie rule relies on.
+ * world_rank[prim] = position of the triangle in the left-to-right leaf order of the reference
+ * world BVH (Source/BVH.cpp:16-34). light_order[i] = prim id of the i-th light triangle in the
+ * lights BVH's leaf order; returns their count through n_light_tris (pass NULL arrays to size). */
+int prt_scene_reference_order(const prt_scene* scene, int64_t* world_rank, int64_t* light_order,
+                              int64_t* n_light_tris);
+
+/* ---- ray queries: replaces Hittable::Hit on `world` (Source/Hittable.h:34) --------------------- */
+/* origins/directions: [n][3] doubles; tmin/tmax: [n] (Interval, inclusive — Source/Interval.h:21).
+ * prim[i] = -1 on miss (t/alpha/beta then untouched = 0). alpha/beta are the barycentrics of v1/v2
+ * (Source/Triangle.cpp:70-71). Host pointers; copies are part of the call. */
+int prt_trace_closest(prt_scene* scene, int64_t n, const double* origins, const double* directions,
+                      const double* tmin, const double* tmax, int32_t* prim, double* t,
+                      double* alpha, double* beta);
+/* hit[i] = 1 iff some triangle is hit inside [tmin, tmax] (the visibility query of
+ * Source/Camera.cpp:147-155 phrased as any-hit). */
+int prt_trace_any(prt_scene* scene, int64_t n, const double* origins, const double* directions,
+                  const double* tmin, const double* tmax, uint8_t* hit);
+/* Same, all pointers in device memory of the context's GPU, launched on `stream` (a cudaStream_t
+ * passed as void*; NULL = the context's stream). Asynchronous. */
+int prt_trace_closest_device(prt_scene* scene, int64_t n, const double* origins,
+                             const double* directions, const double* tmin, const double* tmax,
+                             int32_t* prim, double* t, double* alpha, double* beta, void* stream);
+int prt_trace_any_device(prt_scene* scene, int64_t n, const double* origins,
+                         const double* directions, const double* tmin, const double* tmax,
+                         uint8_t* hit, void* stream);
+
+/* ---- light sampling: replaces Hittable::Sample on `lights` (Source/Hittable.h:36) -------------- */
+/* u: [n][4] uniforms in draw order (HittableList.h:49, BVH.cpp:64, Triangle.cpp:86 x then y).
+ * Outputs: position[n][3], normal[n][3] (face-forwarded to the origin), front[n], pdf[n],
+ * prim[n] (sampled light triangle). Host pointers. */
+int prt_sample_lights(prt_scene* scene, int64_t n, const double* origins, const double* u,
+                      double* position, double* normal, uint8_t* front, double* pdf,
+                      int32_t* prim);
+
+/* ---- rendering: replaces Camera::Render (Source/Camera.cpp:21-73) ------------------------------ */
+/* rgb: host buffer of image_width*image_height*3 doubles, OVERWRITTEN with the radiance of the
+ * requested sample range scaled by 1/samples_per_pixel (a caller that wants the reference's
+ * accumulate-on-top behaviour, Source/Camera.cpp:81, adds it to its own buffer). */
+int prt_render(prt_scene* scene, const prt_camera* camera, const prt_render_params* params,
+               double* rgb);
+/* Same, ACCUMULATING (+=) into a device buffer and asynchronous on `stream`; the multi-GPU path
+ * reduces these buffers with one NCCL sum (torch.distributed) after every rank has rendered its
+ * sample range. */
+int prt_render_device(prt_scene* scene, const prt_camera* camera,
+                      const prt_render_params* params, double* rgb_device, void* stream);
+
+/* ---- output stage: replaces the pixel loop of Camera::WriteColorAttachment (Camera.cpp:279-331) */
+/* NaN scrub, sRGB OETF, clamp to [0,0.9999]*255 truncation → rgb8[W*H*3]; optional float32 copy
+ * of the scrubbed linear image (the .hdr payload). Device buffer in, host buffers out. */
+int prt_resolve_device(prt_scene* scene, const double* rgb_device, int32_t width, int32_t height,
+                       uint8_t* rgb8, float* rgb32f);
+
+int prt_get_stats(const prt_scene* scene, prt_stats* out);
+/* Waits for all work queued on the context's stream. */
+int prt_synchronize(prt_context* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PRT_B200_H */
