@@ -103,15 +103,17 @@ enum prt_accel {
      * flattened, FP64 boxes, traversed in the reference's order (left then right,
      * Source/BVH.cpp:51-61) including its duplicated span-1 children. Bit-exact by construction. */
     PRT_ACCEL_REFERENCE_BVH2 = 0,
-    /* SAH BVH collapsed to 8-wide nodes with outward-rounded FP32 child boxes, near-to-far
-     * ordered traversal, ties resolved by reference DFS rank (last visited wins,
-     * Source/Interval.h:21-23 + Source/BVH.cpp:58). Same hits, far fewer node visits. */
-    PRT_ACCEL_WIDE_BVH8 = 1
+    /* Binned-SAH BVH2, 64-byte nodes holding both child boxes as outward-rounded FP32, near-first
+     * traversal. Same hits: the triangle test is the reference's FP64 arithmetic, the boxes only
+     * ever contain the reference's boxes, and a ray that meets two triangles at the very same t
+     * (the one case where the reference's visiting order decides: last visited wins,
+     * Source/Interval.h:21-23 + Source/BVH.cpp:58) is re-traced through the reference BVH. */
+    PRT_ACCEL_SAH_BVH2 = 1
 };
 
 typedef struct prt_build_opts {
     int32_t accel;        /* prt_accel */
-    int32_t reserved[7];
+    int32_t reserved[7];  /* reserved[0]: max triangles per SAH leaf (0 = default 4, at most 8) */
 } prt_build_opts;
 
 /* ---- camera + integrator parameters (public fields of Source/Camera.h:14-33) ------------------ */
@@ -226,6 +228,9 @@ int prt_render_device(prt_scene* scene, const prt_camera* camera,
 int prt_resolve_device(prt_scene* scene, const double* rgb_device, int32_t width, int32_t height,
                        uint8_t* rgb8, float* rgb32f);
 
+/* enable != 0: the ray-query and render kernels count BVH node and triangle record fetches
+ * (instrumented instantiations; slower). Read them back through prt_get_stats. */
+int prt_set_counters(prt_scene* scene, int enable);
 int prt_get_stats(const prt_scene* scene, prt_stats* out);
 /* Waits for all work queued on the context's stream. */
 int prt_synchronize(prt_context* ctx);

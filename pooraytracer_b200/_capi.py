@@ -24,7 +24,7 @@ PRT_ERR_UNSUPPORTED = -6
 MAT_LAMBERTIAN, MAT_PHONG, MAT_MIRROR, MAT_COOK_TORRANCE, MAT_DIFFUSE_LIGHT, MAT_DEBUG, MAT_EMPTY = range(7)
 
 ACCEL_REFERENCE_BVH2 = 0
-ACCEL_WIDE_BVH8 = 1
+ACCEL_SAH_BVH2 = 1
 
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
@@ -139,6 +139,7 @@ PROTOTYPES = {
     "prt_render": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p]),
     "prt_render_device": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p, C.c_void_p]),
     "prt_resolve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "prt_set_counters": (C.c_int, [C.c_void_p, C.c_int]),
     "prt_get_stats": (C.c_int, [C.c_void_p, C.POINTER(PrtStats)]),
     "prt_synchronize": (C.c_int, [C.c_void_p]),
 }

@@ -127,7 +127,7 @@ class Context:
 
 
 class Scene:
-    def __init__(self, ctx: Context, data: SceneData, accel: int | None = capi.ACCEL_WIDE_BVH8):
+    def __init__(self, ctx: Context, data: SceneData, accel: int | None = capi.ACCEL_SAH_BVH2):
         self.ctx, self.lib, self.data = ctx, ctx.lib, data
         desc, keep = make_scene_desc(data)
         h = C.c_void_p()
@@ -212,6 +212,9 @@ class Scene:
         f32 = np.empty((height, width, 3), dtype=np.float32) if want_float else None
         _check(self.lib, self.lib.prt_resolve_device(self.handle, C.c_void_p(device_ptr), width, height, _ptr(rgb8), _ptr(f32)))
         return rgb8, f32
+
+    def set_counters(self, enable: bool):
+        _check(self.lib, self.lib.prt_set_counters(self.handle, 1 if enable else 0))
 
     def stats(self) -> capi.PrtStats:
         s = capi.PrtStats()

@@ -1,0 +1,627 @@
+/*
+ * capi.cu — the C ABI of include/prt_b200.h: context / scene lifecycle, uploads, and the host side
+ * of the wavefront (pass scheduling, stats). No CPU fallback: every compute entry point needs the
+ * context's GPU.
+ */
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/prt_b200.h"
+#include "launch.h"
+#include "scene_host.h"
+
+using namespace prt;
+
+namespace {
+thread_local std::string g_last_error = "";
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+}  // namespace
+
+struct prt_context {
+    int device = -1; /* < 0: host-only */
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+};
+
+namespace {
+
+#define CUDA_TRY(expr)                                                                                         \
+    do {                                                                                                       \
+        cudaError_t e__ = (expr);                                                                              \
+        if (e__ != cudaSuccess) {                                                                              \
+            const int code__ = e__ == cudaErrorMemoryAllocation ? PRT_ERR_OUT_OF_MEMORY : PRT_ERR_CUDA;       \
+            return fail(code__, std::string(#expr) + ": " + cudaGetErrorString(e__));                         \
+        }                                                                                                      \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    cudaError_t ensure(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        release();
+        if (count == 0) count = 1;
+        cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        else p = nullptr;
+        return e;
+    }
+    cudaError_t upload(const std::vector<T>& v, cudaStream_t st) {
+        cudaError_t e = ensure(v.size());
+        if (e != cudaSuccess || v.empty()) return e;
+        return cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+    }
+};
+
+}  // namespace
+
+struct prt_scene {
+    prt_context* ctx = nullptr;
+    HostScene host;
+    bool committed = false;
+    int accel = PRT_ACCEL_SAH_BVH2;
+
+    /* HBM-resident scene */
+    DevBuf<TriIsect> d_tris;
+    DevBuf<int32_t> d_slot_prim;
+    DevBuf<TriShade> d_shade;
+    DevBuf<Node2> d_nodes2;
+    DevBuf<RefNode> d_ref_nodes;
+    DevBuf<LightTri> d_light_tris;
+    DevBuf<LightNode> d_light_nodes;
+    DevBuf<DevMaterial> d_materials;
+    DevBuf<DevTexture> d_textures;
+    DevBuf<uint8_t> d_texels;
+    DevBuf<double> d_srgb;
+    DevBuf<uint8_t> d_prim_class;
+    DevScene dev;
+
+    /* scratch for the host-pointer entry points */
+    DevBuf<double> s_o, s_d, s_tmin, s_tmax, s_t, s_a, s_b, s_u, s_pos, s_nrm, s_pdf;
+    DevBuf<int32_t> s_prim;
+    DevBuf<uint8_t> s_hit;
+    DevBuf<int32_t> d_fetch;             /* work cursor of the ray-query kernels */
+    DevBuf<unsigned long long> d_counters; /* [2] node visits, triangle tests */
+    DevBuf<double> s_rgb;
+    DevBuf<uint8_t> s_rgb8;
+    DevBuf<float> s_rgb32f;
+
+    /* wavefront pool */
+    DevBuf<double> p_ray, p_T, p_L, p_hit, p_shadow;
+    DevBuf<int32_t> p_hit_prim, p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qs;
+    DevBuf<uint32_t> p_dim, p_flags;
+    DevBuf<BounceCtrl> p_ctrl;
+    int64_t pool_cap = 0;
+    int pool_bounces = 0;
+
+    bool count_visits = false;
+    prt_stats stats;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timing_pending = false, rays_pending = false, visits_pending = false;
+
+    prt_scene() { std::memset(&stats, 0, sizeof(stats)); std::memset(&dev, 0, sizeof(dev)); }
+    ~prt_scene() {
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+    }
+};
+
+namespace {
+
+int need_device(const prt_scene* s) {
+    if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "null scene");
+    if (!s->ctx || s->ctx->device < 0) return fail(PRT_ERR_NO_DEVICE, "this context has no GPU (host-only context): there is no CPU fallback");
+    if (!s->committed) return fail(PRT_ERR_NOT_COMMITTED, "scene not committed: call prt_scene_commit first");
+    cudaError_t e = cudaSetDevice(s->ctx->device);
+    if (e != cudaSuccess) return fail(PRT_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    return PRT_OK;
+}
+
+LaunchConfig launch_config(const prt_context* ctx) {
+    LaunchConfig lc;
+    lc.sm_count = ctx->sm_count;
+    const char* env = std::getenv("PRT_BLOCKS_PER_SM");
+    lc.trace_blocks_per_sm = env ? std::max(1, std::atoi(env)) : 8;
+    return lc;
+}
+
+int64_t pass_path_budget() {
+    const char* env = std::getenv("PRT_PASS_PATHS");
+    int64_t v = env ? std::atoll(env) : (int64_t(1) << 24);
+    if (v < 1024) v = 1024;
+    return v;
+}
+
+int ensure_pool(prt_scene* s, int64_t cap, int n_bounces) {
+    if (cap > s->pool_cap) {
+        CUDA_TRY(s->p_ray.ensure((size_t)cap * 6));
+        CUDA_TRY(s->p_T.ensure((size_t)cap * 3));
+        CUDA_TRY(s->p_L.ensure((size_t)cap * 3));
+        CUDA_TRY(s->p_hit.ensure((size_t)cap * 3));
+        CUDA_TRY(s->p_shadow.ensure((size_t)cap * 7));
+        CUDA_TRY(s->p_hit_prim.ensure((size_t)cap));
+        CUDA_TRY(s->p_q0.ensure((size_t)cap));
+        CUDA_TRY(s->p_q1.ensure((size_t)cap));
+        CUDA_TRY(s->p_qm0.ensure((size_t)cap));
+        CUDA_TRY(s->p_qm1.ensure((size_t)cap));
+        CUDA_TRY(s->p_qm2.ensure((size_t)cap));
+        CUDA_TRY(s->p_qs.ensure((size_t)cap));
+        CUDA_TRY(s->p_dim.ensure((size_t)cap));
+        CUDA_TRY(s->p_flags.ensure((size_t)cap));
+        s->pool_cap = cap;
+    }
+    if (n_bounces + 2 > s->pool_bounces) {
+        CUDA_TRY(s->p_ctrl.ensure((size_t)n_bounces + 2));
+        s->pool_bounces = n_bounces + 2;
+    }
+    return PRT_OK;
+}
+
+PathBuffers path_buffers(prt_scene* s) {
+    PathBuffers pb;
+    pb.cap = s->pool_cap;
+    pb.ray = s->p_ray.p; pb.T = s->p_T.p; pb.L = s->p_L.p; pb.hit = s->p_hit.p;
+    pb.hit_prim = s->p_hit_prim.p; pb.shadow = s->p_shadow.p; pb.dim = s->p_dim.p; pb.flags = s->p_flags.p;
+    pb.q_extend[0] = s->p_q0.p; pb.q_extend[1] = s->p_q1.p;
+    pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p;
+    pb.q_shadow = s->p_qs.p;
+    pb.ctrl = s->p_ctrl.p;
+    pb.counters = s->count_visits ? s->d_counters.p : nullptr;
+    return pb;
+}
+
+/* Camera::Initialize, Source/Camera.cpp:75-106 (host libm tan, the function the reference calls) */
+void camera_setup(const prt_camera* c, RenderConst& rc) {
+    const int W = c->image_width < 1 ? 1 : c->image_width;
+    const int H = c->image_height < 1 ? 1 : c->image_height;
+    const double aspect = double(W) / double(H);
+    const d3 eye = mk3(c->eye[0], c->eye[1], c->eye[2]), look = mk3(c->look_at[0], c->look_at[1], c->look_at[2]);
+    const d3 up = mk3(c->up[0], c->up[1], c->up[2]);
+    const double focal = length(eye - look);
+    const double theta = c->fovy * 0.01745329251994329576923690768489; /* glm::radians */
+    const double h = std::tan(theta / 2.0);
+    const double vh = 2. * h * focal;
+    const double vw = vh * aspect;
+    const d3 w = normalize(eye - look);
+    const d3 u = normalize(cross(up, w));
+    const d3 v = cross(w, u);
+    const d3 vu = vw * u;
+    const d3 vv = vh * (-v);
+    rc.width = W; rc.height = H; rc.npix = W * H;
+    rc.center = eye;
+    rc.dU = vu / (double)W;
+    rc.dV = vv / (double)H;
+    const d3 upper_left = eye - (focal * w) - vu / 2. - vv / 2.;
+    rc.pixel00 = upper_left + 0.5 * (rc.dU + rc.dV);
+}
+
+}  // namespace
+
+extern "C" {
+
+int prt_abi_version(void) { return PRT_ABI_VERSION; }
+const char* prt_last_error(void) { return g_last_error.c_str(); }
+
+int prt_context_create(int device, prt_context** out) {
+    if (!out) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_context_create: out is null");
+    *out = nullptr;
+    prt_context* c = new (std::nothrow) prt_context();
+    if (!c) return fail(PRT_ERR_OUT_OF_MEMORY, "prt_context_create: out of host memory");
+    if (device >= 0) {
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess || device >= n) {
+            delete c;
+            return fail(PRT_ERR_NO_DEVICE, e != cudaSuccess ? std::string("no CUDA device: ") + cudaGetErrorString(e)
+                                                             : "device index out of range");
+        }
+        cudaDeviceProp prop;
+        e = cudaGetDeviceProperties(&prop, device);
+        if (e != cudaSuccess) { delete c; return fail(PRT_ERR_CUDA, cudaGetErrorString(e)); }
+        if (prop.major != 10) {
+            delete c;
+            return fail(PRT_ERR_NO_DEVICE, std::string("device is sm_") + std::to_string(prop.major) + std::to_string(prop.minor) +
+                                               ", this library carries sm_100a code only");
+        }
+        e = cudaSetDevice(device);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { delete c; return fail(PRT_ERR_CUDA, cudaGetErrorString(e)); }
+        c->sm_count = prop.multiProcessorCount;
+        c->device = device;
+    }
+    *out = c;
+    return PRT_OK;
+}
+
+void prt_context_destroy(prt_context* ctx) {
+    if (!ctx) return;
+    if (ctx->device >= 0) {
+        cudaSetDevice(ctx->device);
+        if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    }
+    delete ctx;
+}
+
+int prt_scene_create(prt_context* ctx, const prt_scene_desc* desc, prt_scene** out) {
+    if (!ctx || !desc || !out) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_scene_create: null argument");
+    *out = nullptr;
+    prt_scene* s = new (std::nothrow) prt_scene();
+    if (!s) return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_create: out of host memory");
+    s->ctx = ctx;
+    try {
+        if (!s->host.ingest(desc)) {
+            std::string msg = s->host.error;
+            delete s;
+            return fail(PRT_ERR_INVALID_ARGUMENT, msg);
+        }
+        s->host.build_reference_bvhs(default_host_threads());
+    } catch (const std::bad_alloc&) {
+        delete s;
+        return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_create: out of host memory");
+    }
+    *out = s;
+    return PRT_OK;
+}
+
+void prt_scene_destroy(prt_scene* scene) {
+    if (!scene) return;
+    if (scene->ctx && scene->ctx->device >= 0) cudaSetDevice(scene->ctx->device);
+    delete scene;
+}
+
+int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
+    if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_scene_commit: null scene");
+    const int accel = opts ? opts->accel : PRT_ACCEL_SAH_BVH2;
+    if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2) return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
+    HostScene& h = s->host;
+    for (size_t m = 0; m < h.mesh_material.size(); ++m)
+        if (h.mesh_first[m + 1] > h.mesh_first[m] && h.materials[h.mesh_material[m]].type == PRT_MAT_COOK_TORRANCE)
+            return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: CookTorrance (Source/Material.h:368-521) is not implemented yet");
+    try {
+        int max_leaf = opts && opts->reserved[0] > 0 ? opts->reserved[0] : 4;
+        if (accel == PRT_ACCEL_SAH_BVH2) h.build_sah_bvh2(default_host_threads(), max_leaf);
+        else h.use_reference_slots();
+        h.flatten_reference_world();
+    } catch (const std::bad_alloc&) {
+        return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_commit: out of host memory");
+    }
+    s->accel = accel;
+    s->stats.node_bytes = accel == PRT_ACCEL_SAH_BVH2 ? PRT_NODE2_BYTES : PRT_REFNODE_BYTES;
+    s->stats.tri_bytes = PRT_TRI_BYTES;
+    s->stats.n_nodes = accel == PRT_ACCEL_SAH_BVH2 ? (int64_t)h.nodes2.size() : (int64_t)h.ref_flat.size();
+    s->stats.n_triangles = h.n_tris;
+    if (s->ctx->device < 0) { /* host-only context: flattening done, nothing to upload */
+        s->committed = true;
+        return PRT_OK;
+    }
+    CUDA_TRY(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = s->ctx->stream;
+    std::vector<uint8_t> prim_class((size_t)h.n_tris);
+    for (int64_t p = 0; p < h.n_tris; ++p) {
+        const DevMaterial& m = h.dev_materials[h.shade[p].material];
+        uint8_t c;
+        if (m.has_emission) c = CLS_EMISSIVE;
+        else if (m.type == PRT_MAT_LAMBERTIAN) c = CLS_LAMBERT;
+        else if (m.type == PRT_MAT_PHONG) c = CLS_PHONG;
+        else if (m.type == PRT_MAT_MIRROR) c = CLS_MIRROR;
+        else if (m.type == PRT_MAT_EMPTY) c = CLS_EMPTY;
+        else c = CLS_LAMBERT; /* unknown types fall back to Lambertian like Model.cpp:282-285 */
+        prim_class[p] = c;
+    }
+    std::vector<double> lut(h.srgb_lut, h.srgb_lut + 256);
+    CUDA_TRY(s->d_tris.upload(h.isect_slots, st));
+    CUDA_TRY(s->d_slot_prim.upload(h.slot_prim, st));
+    CUDA_TRY(s->d_shade.upload(h.shade, st));
+    CUDA_TRY(s->d_nodes2.upload(h.nodes2, st));
+    CUDA_TRY(s->d_ref_nodes.upload(h.ref_flat, st));
+    CUDA_TRY(s->d_light_tris.upload(h.light_tris, st));
+    CUDA_TRY(s->d_light_nodes.upload(h.light_nodes, st));
+    CUDA_TRY(s->d_materials.upload(h.dev_materials, st));
+    CUDA_TRY(s->d_textures.upload(h.dev_textures, st));
+    CUDA_TRY(s->d_texels.upload(h.texel_pool, st));
+    CUDA_TRY(s->d_srgb.upload(lut, st));
+    CUDA_TRY(s->d_prim_class.upload(prim_class, st));
+    CUDA_TRY(s->d_fetch.ensure(4));
+    CUDA_TRY(s->d_counters.ensure(4));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    DevScene& D = s->dev;
+    D.tris = s->d_tris.p;
+    D.slot_prim = s->d_slot_prim.p;
+    D.shade = s->d_shade.p;
+    D.nodes2 = accel == PRT_ACCEL_SAH_BVH2 && !h.nodes2.empty() ? s->d_nodes2.p : nullptr;
+    D.ref_nodes = s->d_ref_nodes.p;
+    D.ref_root = h.ref_root_flat;
+    D.n_nodes2 = (int32_t)h.nodes2.size();
+    D.n_tris = h.n_tris;
+    D.light_tris = s->d_light_tris.p;
+    D.light_nodes = s->d_light_nodes.p;
+    D.light_root = h.light_root_flat;
+    D.n_light_tris = (int32_t)h.light_tris.size();
+    D.lights_area = h.lights_area;
+    D.materials = s->d_materials.p;
+    D.textures = s->d_textures.p;
+    D.texels = s->d_texels.p;
+    D.srgb_lut = s->d_srgb.p;
+    D.n_materials = (int32_t)h.dev_materials.size();
+    D.n_textures = (int32_t)h.dev_textures.size();
+    if (!s->ev0) {
+        CUDA_TRY(cudaEventCreate(&s->ev0));
+        CUDA_TRY(cudaEventCreate(&s->ev1));
+    }
+    s->committed = true;
+    return PRT_OK;
+}
+
+int prt_scene_reference_order(const prt_scene* s, int64_t* world_rank, int64_t* light_order, int64_t* n_light_tris) {
+    if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "null scene");
+    if (world_rank) std::copy(s->host.world_rank.begin(), s->host.world_rank.end(), world_rank);
+    if (light_order) std::copy(s->host.light_order.begin(), s->host.light_order.end(), light_order);
+    if (n_light_tris) *n_light_tris = (int64_t)s->host.light_order.size();
+    return PRT_OK;
+}
+
+int prt_set_counters(prt_scene* s, int enable) {
+    if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "null scene");
+    s->count_visits = enable != 0;
+    return PRT_OK;
+}
+
+/* ---- ray queries ----------------------------------------------------------------------------- */
+static int trace_begin(prt_scene* s, int64_t n, cudaStream_t st) {
+    if (n < 0 || n >= (int64_t(1) << 31) - 64) return fail(PRT_ERR_INVALID_ARGUMENT, "ray count out of range");
+    CUDA_TRY(cudaMemsetAsync(s->d_fetch.p, 0, 4 * sizeof(int32_t), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaEventRecord(s->ev0, st));
+    return PRT_OK;
+}
+static int trace_end(prt_scene* s, int64_t n, bool shadow, cudaStream_t st) {
+    CUDA_TRY(cudaEventRecord(s->ev1, st));
+    CUDA_TRY(cudaGetLastError());
+    s->timing_pending = true;
+    s->rays_pending = false;
+    s->visits_pending = s->count_visits;
+    s->stats.node_visits = s->stats.tri_tests = 0;
+    s->stats.extend_rays = shadow ? 0 : (uint64_t)n;
+    s->stats.shadow_rays = shadow ? (uint64_t)n : 0;
+    s->stats.paths = 0;
+    s->stats.kernel_launches = n > 0 ? 1 : 0;
+    return PRT_OK;
+}
+
+int prt_trace_closest_device(prt_scene* s, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
+                             int32_t* prim, double* t, double* alpha, double* beta, void* stream) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (n > 0 && (!o || !d || !tmin || !tmax || !prim)) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_closest: null array");
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->ctx->stream;
+    rc = trace_begin(s, n, st);
+    if (rc) return rc;
+    launch_trace_closest(s->dev, n, o, d, tmin, tmax, prim, t, alpha, beta, s->d_fetch.p, s->count_visits ? s->d_counters.p : nullptr,
+                         launch_config(s->ctx), st);
+    return trace_end(s, n, false, st);
+}
+
+int prt_trace_any_device(prt_scene* s, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
+                         uint8_t* hit, void* stream) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (n > 0 && (!o || !d || !tmin || !tmax || !hit)) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_any: null array");
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->ctx->stream;
+    rc = trace_begin(s, n, st);
+    if (rc) return rc;
+    launch_trace_any(s->dev, n, o, d, tmin, tmax, hit, s->d_fetch.p, s->count_visits ? s->d_counters.p : nullptr, launch_config(s->ctx), st);
+    return trace_end(s, n, true, st);
+}
+
+int prt_trace_closest(prt_scene* s, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
+                      int32_t* prim, double* t, double* alpha, double* beta) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (n > 0 && (!o || !d || !tmin || !tmax || !prim)) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_closest: null array");
+    if (n <= 0) return PRT_OK;
+    cudaStream_t st = s->ctx->stream;
+    const size_t N = (size_t)n;
+    CUDA_TRY(s->s_o.ensure(3 * N)); CUDA_TRY(s->s_d.ensure(3 * N)); CUDA_TRY(s->s_tmin.ensure(N)); CUDA_TRY(s->s_tmax.ensure(N));
+    CUDA_TRY(s->s_prim.ensure(N)); CUDA_TRY(s->s_t.ensure(N)); CUDA_TRY(s->s_a.ensure(N)); CUDA_TRY(s->s_b.ensure(N));
+    CUDA_TRY(cudaMemcpyAsync(s->s_o.p, o, 3 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(s->s_d.p, d, 3 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(s->s_tmin.p, tmin, N * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(s->s_tmax.p, tmax, N * sizeof(double), cudaMemcpyHostToDevice, st));
+    rc = prt_trace_closest_device(s, n, s->s_o.p, s->s_d.p, s->s_tmin.p, s->s_tmax.p, s->s_prim.p, s->s_t.p, s->s_a.p, s->s_b.p, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(prim, s->s_prim.p, N * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    if (t) CUDA_TRY(cudaMemcpyAsync(t, s->s_t.p, N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (alpha) CUDA_TRY(cudaMemcpyAsync(alpha, s->s_a.p, N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (beta) CUDA_TRY(cudaMemcpyAsync(beta, s->s_b.p, N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return PRT_OK;
+}
+
+int prt_trace_any(prt_scene* s, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax, uint8_t* hit) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (n > 0 && (!o || !d || !tmin || !tmax || !hit)) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_any: null array");
+    if (n <= 0) return PRT_OK;
+    cudaStream_t st = s->ctx->stream;
+    const size_t N = (size_t)n;
+    CUDA_TRY(s->s_o.ensure(3 * N)); CUDA_TRY(s->s_d.ensure(3 * N)); CUDA_TRY(s->s_tmin.ensure(N)); CUDA_TRY(s->s_tmax.ensure(N));
+    CUDA_TRY(s->s_hit.ensure(N));
+    CUDA_TRY(cudaMemcpyAsync(s->s_o.p, o, 3 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(s->s_d.p, d, 3 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(s->s_tmin.p, tmin, N * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(s->s_tmax.p, tmax, N * sizeof(double), cudaMemcpyHostToDevice, st));
+    rc = prt_trace_any_device(s, n, s->s_o.p, s->s_d.p, s->s_tmin.p, s->s_tmax.p, s->s_hit.p, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(hit, s->s_hit.p, N, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return PRT_OK;
+}
+
+int prt_sample_lights(prt_scene* s, int64_t n, const double* origins, const double* u, double* position, double* normal,
+                      uint8_t* front, double* pdf, int32_t* prim) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (s->dev.light_root < 0) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_sample_lights: the scene has no emissive mesh");
+    if (n > 0 && (!origins || !u || !position || !normal || !front || !pdf || !prim)) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_sample_lights: null array");
+    if (n <= 0) return PRT_OK;
+    cudaStream_t st = s->ctx->stream;
+    const size_t N = (size_t)n;
+    CUDA_TRY(s->s_o.ensure(3 * N)); CUDA_TRY(s->s_u.ensure(4 * N)); CUDA_TRY(s->s_pos.ensure(3 * N)); CUDA_TRY(s->s_nrm.ensure(3 * N));
+    CUDA_TRY(s->s_hit.ensure(N)); CUDA_TRY(s->s_pdf.ensure(N)); CUDA_TRY(s->s_prim.ensure(N));
+    CUDA_TRY(cudaMemcpyAsync(s->s_o.p, origins, 3 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(s->s_u.p, u, 4 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+    launch_sample_lights(s->dev, n, s->s_o.p, s->s_u.p, s->s_pos.p, s->s_nrm.p, s->s_hit.p, s->s_pdf.p, s->s_prim.p, st);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(position, s->s_pos.p, 3 * N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(normal, s->s_nrm.p, 3 * N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(front, s->s_hit.p, N, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(pdf, s->s_pdf.p, N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(prim, s->s_prim.p, N * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return PRT_OK;
+}
+
+/* ---- rendering ------------------------------------------------------------------------------- */
+int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_params* params, double* rgb_device, void* stream) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (!camera || !params || !rgb_device) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_render: null argument");
+    if (params->samples_per_pixel < 1 || params->max_depth < 0 || params->max_depth > 100000)
+        return fail(PRT_ERR_INVALID_ARGUMENT, "prt_render: samples_per_pixel < 1 or max_depth out of range");
+    if (params->sample_lights && s->dev.light_root < 0)
+        return fail(PRT_ERR_INVALID_ARGUMENT, "prt_render: sample_lights is set but the scene has no emissive mesh");
+    int sb = params->spp_begin, se = params->spp_end;
+    if (sb == 0 && se == 0) se = params->samples_per_pixel;
+    if (sb < 0 || se < sb) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_render: bad sample range");
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->ctx->stream;
+
+    RenderConst rcn;
+    std::memset(&rcn, 0, sizeof(rcn));
+    camera_setup(camera, rcn);
+    if ((int64_t)rcn.width * rcn.height >= (int64_t(1) << 31) / 4) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_render: image too large");
+    rcn.max_depth = params->max_depth;
+    rcn.sample_lights = params->sample_lights ? 1 : 0;
+    rcn.flags = params->flags | (s->count_visits ? PRT_RENDER_COUNTERS : 0u);
+    rcn.rr = params->russian_roulette;
+    rcn.scale = 1.0 / params->samples_per_pixel;
+    for (int k = 0; k < 3; ++k) rcn.background[k] = params->background[k];
+    rcn.rng_key = params->rng_key;
+
+    const int64_t budget = pass_path_budget();
+    int per_pass = (int)std::max<int64_t>(1, budget / rcn.npix);
+    per_pass = std::min(per_pass, std::max(1, se - sb));
+    const int n_bounces = params->max_depth + 1;
+    rc = ensure_pool(s, (int64_t)per_pass * rcn.npix, n_bounces);
+    if (rc) return rc;
+    const bool counting = (rcn.flags & PRT_RENDER_COUNTERS) != 0;
+    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
+    PathBuffers pb = path_buffers(s);
+    pb.counters = counting ? s->d_counters.p : nullptr;
+    const LaunchConfig lc = launch_config(s->ctx);
+    uint64_t launches = 0;
+    CUDA_TRY(cudaEventRecord(s->ev0, st));
+    for (int s0 = sb; s0 < se; s0 += per_pass) {
+        rcn.sample_first = s0;
+        rcn.n_samples = std::min(per_pass, se - s0);
+        rcn.n_paths = rcn.n_samples * rcn.npix;
+        launches += (uint64_t)launch_render_pass(s->dev, s->d_prim_class.p, rcn, pb, rgb_device, s->d_counters.p, lc, st);
+        CUDA_TRY(cudaGetLastError());
+    }
+    CUDA_TRY(cudaEventRecord(s->ev1, st));
+    s->timing_pending = true;
+    s->rays_pending = true;
+    s->visits_pending = counting;
+    s->stats.extend_rays = 0;
+    s->stats.shadow_rays = 0;
+    s->stats.node_visits = 0;
+    s->stats.tri_tests = 0;
+    s->stats.paths = (uint64_t)rcn.npix * (uint64_t)(se - sb);
+    s->stats.kernel_launches = launches;
+    return PRT_OK;
+}
+
+int prt_render(prt_scene* s, const prt_camera* camera, const prt_render_params* params, double* rgb) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (!camera || !params || !rgb) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_render: null argument");
+    const int W = camera->image_width < 1 ? 1 : camera->image_width, H = camera->image_height < 1 ? 1 : camera->image_height;
+    const size_t n = (size_t)W * H * 3;
+    cudaStream_t st = s->ctx->stream;
+    CUDA_TRY(s->s_rgb.ensure(n));
+    CUDA_TRY(cudaMemsetAsync(s->s_rgb.p, 0, n * sizeof(double), st));
+    rc = prt_render_device(s, camera, params, s->s_rgb.p, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(rgb, s->s_rgb.p, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return PRT_OK;
+}
+
+int prt_resolve_device(prt_scene* s, const double* rgb_device, int32_t width, int32_t height, uint8_t* rgb8, float* rgb32f) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (!rgb_device || width < 1 || height < 1) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_resolve_device: bad argument");
+    const size_t n = (size_t)width * height * 3;
+    cudaStream_t st = s->ctx->stream;
+    if (rgb8) CUDA_TRY(s->s_rgb8.ensure(n));
+    if (rgb32f) CUDA_TRY(s->s_rgb32f.ensure(n));
+    launch_resolve(rgb_device, (int64_t)width * height, rgb8 ? s->s_rgb8.p : nullptr, rgb32f ? s->s_rgb32f.p : nullptr, st);
+    CUDA_TRY(cudaGetLastError());
+    if (rgb8) CUDA_TRY(cudaMemcpyAsync(rgb8, s->s_rgb8.p, n, cudaMemcpyDeviceToHost, st));
+    if (rgb32f) CUDA_TRY(cudaMemcpyAsync(rgb32f, s->s_rgb32f.p, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return PRT_OK;
+}
+
+int prt_get_stats(const prt_scene* cs, prt_stats* out) {
+    if (!cs || !out) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_get_stats: null argument");
+    prt_scene* s = const_cast<prt_scene*>(cs);
+    if (s->ctx && s->ctx->device >= 0 && s->committed) {
+        cudaSetDevice(s->ctx->device);
+        if (s->timing_pending) {
+            if (cudaEventSynchronize(s->ev1) == cudaSuccess) {
+                float ms = 0.f;
+                if (cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) s->stats.gpu_ms = ms;
+            }
+            s->timing_pending = false;
+        }
+        if (s->rays_pending || s->visits_pending) {
+            unsigned long long c[4] = {0, 0, 0, 0};
+            if (cudaMemcpy(c, s->d_counters.p, sizeof(c), cudaMemcpyDeviceToHost) == cudaSuccess) {
+                if (s->visits_pending) { s->stats.node_visits = c[0]; s->stats.tri_tests = c[1]; }
+                if (s->rays_pending) { s->stats.extend_rays = c[2]; s->stats.shadow_rays = c[3]; }
+            }
+            s->rays_pending = s->visits_pending = false;
+        }
+    }
+    *out = s->stats;
+    return PRT_OK;
+}
+
+int prt_synchronize(prt_context* ctx) {
+    if (!ctx) return fail(PRT_ERR_INVALID_ARGUMENT, "null context");
+    if (ctx->device < 0) return PRT_OK;
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return PRT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,662 @@
+/*
+ * scene_host.cpp — host flattener: triangle records, the reference's median-split BVHs (needed for
+ * the tie rule and for light sampling whatever acceleration structure is traversed), the SAH BVH2
+ * the extend / shadow kernels walk, and the tables for materials, textures and lights.
+ *
+ * Reference behaviour restated here (paths relative to /root/reference/):
+ *   Triangle::Triangle            Source/Triangle.cpp:11-53      make_triangle()
+ *   Triangle::SetBoundingBox      Source/Triangle.cpp:94-99      make_triangle()
+ *   AABB ctors / PadToMinimus     Source/AABB.cpp:16-29,76-82    box_of_points(), box_union()
+ *   BVHNode::BVHNode              Source/BVH.cpp:7-48,68-73      RefBuilder::build()
+ *   world / lights assembly       main.cpp:36-45                 build_reference_bvhs()
+ *   PhoneReflectance probabilities Source/Material.h:318-327     ingest()
+ *   ImageTexture::SRGBToLinear    Source/Texture.cpp:66-71       ingest() (256-entry table)
+ */
+#include "scene_host.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <limits>
+#include <thread>
+
+namespace prt {
+
+namespace {
+
+const double INF = std::numeric_limits<double>::infinity();
+
+/* ---- Interval / AABB in the reference's own construction order --------------------------------- */
+inline void interval_union(double amin, double amax, double bmin, double bmax, double& omin, double& omax) {
+    omin = amin <= bmin ? amin : bmin; /* Interval.h:13-16 */
+    omax = amax >= bmax ? amax : bmax;
+}
+inline Box6 box_empty() {
+    Box6 b;
+    for (int a = 0; a < 3; ++a) { b.v[2 * a] = +INF; b.v[2 * a + 1] = -INF; }
+    return b;
+}
+inline Box6 box_union(const Box6& a, const Box6& b) { /* AABB.cpp:24-29: no re-padding */
+    Box6 r;
+    for (int k = 0; k < 3; ++k) interval_union(a.v[2 * k], a.v[2 * k + 1], b.v[2 * k], b.v[2 * k + 1], r.v[2 * k], r.v[2 * k + 1]);
+    return r;
+}
+inline Box6 box_of_points(d3 a, d3 b) { /* AABB.cpp:16-22 + 76-82 */
+    Box6 r;
+    const double pa[3] = {a.x, a.y, a.z}, pb[3] = {b.x, b.y, b.z};
+    for (int k = 0; k < 3; ++k) {
+        double lo = pa[k] <= pb[k] ? pa[k] : pb[k];
+        double hi = pa[k] <= pb[k] ? pb[k] : pa[k];
+        const double delta = 0.0001;
+        if (hi - lo < delta) { /* Interval::Expand, Interval.h:33-36 */
+            const double padding = delta / 2.;
+            lo = lo - padding;
+            hi = hi + padding;
+        }
+        r.v[2 * k] = lo;
+        r.v[2 * k + 1] = hi;
+    }
+    return r;
+}
+inline int longest_axis(const Box6& b) { /* AABB.cpp:66-74 */
+    const double lx = b.v[1] - b.v[0], ly = b.v[3] - b.v[2], lz = b.v[5] - b.v[4];
+    if (lx > ly) return lx > lz ? 0 : 2;
+    return ly > lz ? 1 : 2;
+}
+
+/* Triangle::Triangle */
+void make_triangle(const double* pv, const double* pn, const double* puv, TriIsect& I, TriShade& S, double& area, Box6& box) {
+    d3 v0 = mk3(pv[0], pv[1], pv[2]), v1 = mk3(pv[3], pv[4], pv[5]), v2 = mk3(pv[6], pv[7], pv[8]);
+    d2 uv0 = mk2(puv[0], puv[1]), uv1 = mk2(puv[2], puv[3]), uv2 = mk2(puv[4], puv[5]);
+    d3 e0 = v1 - v0, e1 = v2 - v0;
+    d3 n = cross(e0, e1);
+    d3 normal = normalize(n);
+    if (anynan(normal)) {
+        d3 n0 = pn ? mk3(pn[0], pn[1], pn[2]) : mk3(0, 0, 0);
+        d3 n1 = pn ? mk3(pn[3], pn[4], pn[5]) : mk3(0, 0, 0);
+        d3 n2 = pn ? mk3(pn[6], pn[7], pn[8]) : mk3(0, 0, 0);
+        normal = normalize(n0 + n1 + n2);
+        if (anynan(normal)) normal = mk3(0.0, 0.0, 1.0);
+    }
+    d2 du0 = uv1 - uv0, du1 = uv2 - uv0;
+    double f = 1.0 / (du0.x * du1.y - du1.x * du0.y);
+    d3 tangent;
+    tangent.x = f * (du1.y * e0.x - du0.y * e1.x);
+    tangent.y = f * (du1.y * e0.y - du0.y * e1.y);
+    tangent.z = f * (du1.y * e0.z - du0.y * e1.z);
+    tangent = normalize(tangent);
+    if (anynan(tangent)) { /* `abs(v.x) < 0.9f`: the literal is a float promoted to double */
+        d3 helper = (std::fabs(normal.x) < (double)0.9f) ? mk3(1, 0, 0) : mk3(0, 1, 0);
+        tangent = normalize(cross(normal, helper));
+    }
+    area = length(n) * 0.5;
+    double D = dot(normal, v0);
+    d3 w = n / dot(n, n);
+    box = box_union(box_of_points(v0, v1), box_of_points(v0, v2));
+
+    I.n[0] = normal.x; I.n[1] = normal.y; I.n[2] = normal.z;
+    I.D = D;
+    I.w[0] = w.x; I.w[1] = w.y; I.w[2] = w.z;
+    I.v0[0] = v0.x; I.v0[1] = v0.y; I.v0[2] = v0.z;
+    I.e0[0] = e0.x; I.e0[1] = e0.y; I.e0[2] = e0.z;
+    I.e1[0] = e1.x; I.e1[1] = e1.y; I.e1[2] = e1.z;
+    for (int k = 0; k < 6; ++k) S.uv[k] = puv[k];
+    S.tangent[0] = tangent.x; S.tangent[1] = tangent.y; S.tangent[2] = tangent.z;
+    S.normal[0] = normal.x; S.normal[1] = normal.y; S.normal[2] = normal.z;
+    S.material = 0;
+    for (int k = 0; k < 7; ++k) S.pad[k] = 0;
+}
+
+void parallel_ranges(int64_t n, int n_threads, const std::function<void(int64_t, int64_t)>& body);
+
+}  // namespace
+
+int default_host_threads() {
+    unsigned h = std::thread::hardware_concurrency();
+    if (h == 0) h = 4;
+    if (h > 32) h = 32;
+    return (int)h;
+}
+
+namespace {
+void parallel_ranges(int64_t n, int n_threads, const std::function<void(int64_t, int64_t)>& body) {
+    if (n_threads <= 1 || n < 65536) { body(0, n); return; }
+    std::vector<std::thread> th;
+    const int64_t chunk = (n + n_threads - 1) / n_threads;
+    for (int k = 0; k < n_threads; ++k) {
+        const int64_t b = k * chunk, e = std::min(n, b + chunk);
+        if (b >= e) break;
+        th.emplace_back([=, &body]() { body(b, e); });
+    }
+    for (auto& t : th) t.join();
+}
+}  // namespace
+
+/* ------------------------------------------------------------------------------------------------
+ * ingest: copy the description, derive per-triangle records, material / texture tables
+ * ---------------------------------------------------------------------------------------------- */
+bool HostScene::ingest(const prt_scene_desc* d) {
+    if (!d || d->n_triangles < 0 || d->n_meshes < 0 || d->n_materials < 0 || d->n_textures < 0) {
+        error = "prt_scene_create: negative count in prt_scene_desc";
+        return false;
+    }
+    if (d->n_triangles >= (int64_t(1) << 27)) {
+        error = "prt_scene_create: more than 2^27 triangles";
+        return false;
+    }
+    if (d->n_triangles > 0 && (!d->vertices || !d->mesh_first || !d->mesh_material || d->n_meshes == 0)) {
+        error = "prt_scene_create: triangles without vertices / mesh tables";
+        return false;
+    }
+    n_tris = d->n_triangles;
+    mesh_first.assign(d->mesh_first, d->mesh_first + (d->n_meshes ? d->n_meshes + 1 : 0));
+    mesh_material.assign(d->mesh_material, d->mesh_material + d->n_meshes);
+    if (d->n_meshes) {
+        if (mesh_first.front() != 0 || mesh_first.back() != n_tris) {
+            error = "prt_scene_create: mesh_first must run from 0 to n_triangles";
+            return false;
+        }
+        for (int m = 0; m < d->n_meshes; ++m) {
+            if (mesh_first[m + 1] < mesh_first[m]) { error = "prt_scene_create: mesh_first not monotone"; return false; }
+            if (mesh_material[m] < 0 || mesh_material[m] >= d->n_materials) { error = "prt_scene_create: mesh_material out of range"; return false; }
+        }
+    }
+    materials.assign(d->materials, d->materials + d->n_materials);
+    vertices.assign(d->vertices, d->vertices + 9 * n_tris);
+    texcoords.resize((size_t)6 * n_tris);
+    const double uv_default[6] = {0, 0, 1, 0, 1, 1}; /* Model.cpp:170-175 */
+    for (int64_t f = 0; f < n_tris; ++f)
+        std::memcpy(&texcoords[6 * f], d->texcoords ? d->texcoords + 6 * f : uv_default, 6 * sizeof(double));
+
+    /* textures: texel pool + the sRGB table. GetPixel (Texture.cpp:50-65) feeds SRGBToLinear with
+     * colorScale * byte; the 256 possible results are computed here with the host libm `pow`,
+     * which is the very function the reference calls, so the table holds the reference's bits. */
+    const double colorScale = 1.0 / 255.0;
+    for (int i = 0; i < 256; ++i) {
+        const double v = colorScale * (double)i;
+        srgb_lut[i] = (v <= 0.04045) ? v * (1. / 12.92) : std::pow((v + 0.055) * (1. / 1.055), 2.4);
+    }
+    textures.clear();
+    dev_textures.clear();
+    texel_pool.clear();
+    for (int i = 0; i < d->n_textures; ++i) {
+        const prt_texture& pt = d->textures[i];
+        HostTexture t;
+        DevTexture dt;
+        dt.offset = (int64_t)texel_pool.size();
+        dt.width = dt.height = dt.channels = dt.valid = 0;
+        if (pt.texels && pt.width > 0 && pt.height > 0 && pt.channels > 0) {
+            t.width = pt.width; t.height = pt.height; t.channels = pt.channels;
+            const size_t nb = (size_t)pt.width * pt.height * pt.channels;
+            t.texels.assign(pt.texels, pt.texels + nb);
+            texel_pool.insert(texel_pool.end(), t.texels.begin(), t.texels.end());
+            while (texel_pool.size() % 16) texel_pool.push_back(0);
+            dt.width = pt.width; dt.height = pt.height; dt.channels = pt.channels; dt.valid = 1;
+        }
+        textures.push_back(std::move(t));
+        dev_textures.push_back(dt);
+    }
+
+    dev_materials.clear();
+    for (int i = 0; i < d->n_materials; ++i) {
+        const prt_material& pm = materials[i];
+        DevMaterial m;
+        std::memset(&m, 0, sizeof(m));
+        for (int k = 0; k < 3; ++k) { m.kd[k] = pm.kd[k]; m.ks[k] = pm.ks[k]; }
+        m.type = pm.type;
+        m.kd_tex = (pm.kd_tex >= 0 && pm.kd_tex < d->n_textures) ? pm.kd_tex : -1;
+        m.ns = pm.ns;
+        if (pm.ns <= 9.) { m.pkd = 1.0; m.pks = 0.0; } else { m.pkd = 0.6; m.pks = 0.4; } /* Material.h:318-327 */
+        m.has_emission = (pm.type == PRT_MAT_DIFFUSE_LIGHT || pm.type == PRT_MAT_DEBUG) ? 1 : 0; /* :166,528 */
+        for (int k = 0; k < 3; ++k) m.emission[k] = pm.type == PRT_MAT_DEBUG ? pm.kd[k] : (pm.type == PRT_MAT_DIFFUSE_LIGHT ? pm.emission[k] : 0.0);
+        if (pm.type == PRT_MAT_PHONG) m.skip_light_sampling = pm.ns > 1. ? 1 : 0; /* Material.h:328 */
+        else m.skip_light_sampling = (pm.type == PRT_MAT_MIRROR || pm.type == PRT_MAT_EMPTY) ? 1 : 0; /* :365,539 */
+        dev_materials.push_back(m);
+    }
+
+    isect.resize((size_t)n_tris);
+    shade.resize((size_t)n_tris);
+    area.resize((size_t)n_tris);
+    tri_box.resize((size_t)n_tris);
+    const double* pn = d->normals;
+    parallel_ranges(n_tris, default_host_threads(), [&](int64_t b, int64_t e) {
+        for (int64_t f = b; f < e; ++f)
+            make_triangle(&vertices[9 * f], pn ? pn + 9 * f : nullptr, &texcoords[6 * f], isect[f], shade[f], area[f], tri_box[f]);
+    });
+    for (size_t m = 0; m + 1 < mesh_first.size(); ++m)
+        for (int64_t f = mesh_first[m]; f < mesh_first[m + 1]; ++f) shade[f].material = mesh_material[m];
+    return true;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * the reference's BVH (median split on the longest axis by bbox.min, std::sort) — BVH.cpp:7-48
+ * ---------------------------------------------------------------------------------------------- */
+namespace {
+
+struct KeyRef {
+    double key;
+    ObjRef ref;
+};
+
+int64_t ref_node_count(int64_t span) { /* nodes a build over `span` objects creates */
+    if (span <= 2) return 1;
+    return 1 + ref_node_count(span / 2) + ref_node_count(span - span / 2);
+}
+
+struct RefBuilder {
+    HostScene& s;
+    std::vector<KeyRef>& items;
+    RefBuilder(HostScene& s, std::vector<KeyRef>& items) : s(s), items(items) {}
+
+    const Box6& box_of(ObjRef o) const { return o.kind == 0 ? s.tri_box[o.idx] : s.ref_nodes[o.idx].box; }
+    double area_of(ObjRef o) const { return o.kind == 0 ? s.area[o.idx] : s.ref_nodes[o.idx].area; }
+
+    /* builds the node `at` over items[start,end); nodes of the subtree occupy [at, at+count) */
+    void build(int64_t start, int64_t end, int32_t at, int par_depth) {
+        HostRefNode node;
+        node.box = box_empty();
+        for (int64_t i = start; i < end; ++i) node.box = box_union(node.box, box_of(items[i].ref));
+        const int axis = longest_axis(node.box);
+        const int64_t span = end - start;
+        if (span == 1) {
+            node.left = node.right = items[start].ref;
+            node.area = area_of(items[start].ref);
+        } else if (span == 2) {
+            node.left = items[start].ref;
+            node.right = items[start + 1].ref;
+            node.area = area_of(items[start].ref) + area_of(items[start + 1].ref);
+        } else {
+            for (int64_t i = start; i < end; ++i) items[i].key = box_of(items[i].ref).v[2 * axis];
+            /* the same libstdc++ std::sort, driven by the same comparison outcomes as
+             * BVH.cpp:31,68-73, leaves the same permutation */
+            std::sort(items.begin() + start, items.begin() + end, [](const KeyRef& a, const KeyRef& b) { return a.key < b.key; });
+            const int64_t mid = start + span / 2;
+            const int32_t l = at + 1;
+            const int32_t r = (int32_t)(at + 1 + ref_node_count(mid - start));
+            if (par_depth > 0 && span > 32768) {
+                std::thread t([&, l]() { build(start, mid, l, par_depth - 1); });
+                build(mid, end, r, par_depth - 1);
+                t.join();
+            } else {
+                build(start, mid, l, 0);
+                build(mid, end, r, 0);
+            }
+            node.left = ObjRef{1, l};
+            node.right = ObjRef{1, r};
+            node.area = s.ref_nodes[l].area + s.ref_nodes[r].area;
+        }
+        s.ref_nodes[at] = node;
+    }
+};
+
+int32_t build_ref_tree(HostScene& s, std::vector<KeyRef>& items, int n_threads) {
+    const int64_t span = (int64_t)items.size();
+    const int32_t at = (int32_t)s.ref_nodes.size();
+    s.ref_nodes.resize(s.ref_nodes.size() + (size_t)ref_node_count(span));
+    int par = 0;
+    while ((1 << par) < n_threads) ++par;
+    RefBuilder b(s, items);
+    b.build(0, span, at, par + 1);
+    return at;
+}
+
+void walk_ref_leaves(const HostScene& s, ObjRef o, std::vector<int32_t>& out) {
+    /* iterative DFS, left before right; a span-1 node (left == right) contributes its leaf once */
+    std::vector<ObjRef> stack{o};
+    while (!stack.empty()) {
+        ObjRef c = stack.back();
+        stack.pop_back();
+        if (c.kind == 0) { out.push_back(c.idx); continue; }
+        const HostRefNode& n = s.ref_nodes[c.idx];
+        if (!(n.right.kind == n.left.kind && n.right.idx == n.left.idx)) stack.push_back(n.right);
+        stack.push_back(n.left);
+    }
+}
+
+}  // namespace
+
+void HostScene::build_reference_bvhs(int n_threads) {
+    ref_nodes.clear();
+    world_root = lights_root = -1;
+    std::vector<ObjRef> world, lights;
+    const int n_meshes = (int)mesh_material.size();
+    for (int m = 0; m < n_meshes; ++m) { /* main.cpp:37-43 */
+        if (mesh_first[m + 1] <= mesh_first[m]) continue;
+        std::vector<KeyRef> items;
+        items.reserve((size_t)(mesh_first[m + 1] - mesh_first[m]));
+        for (int64_t f = mesh_first[m]; f < mesh_first[m + 1]; ++f) items.push_back(KeyRef{0.0, ObjRef{0, (int32_t)f}});
+        /* BVHNode(shared_ptr<Mesh>) sorts mesh->objects IN PLACE (BVH.cpp:49): the second build
+         * for an emissive mesh starts from the order the first one left behind */
+        world.push_back(ObjRef{1, build_ref_tree(*this, items, n_threads)});
+        if (dev_materials[mesh_material[m]].has_emission) lights.push_back(ObjRef{1, build_ref_tree(*this, items, n_threads)});
+    }
+    auto top = [&](std::vector<ObjRef>& list) -> int32_t { /* main.cpp:44-45 */
+        if (list.empty()) return -1;
+        std::vector<KeyRef> items;
+        for (ObjRef o : list) items.push_back(KeyRef{0.0, o});
+        return build_ref_tree(*this, items, 1);
+    };
+    world_root = top(world);
+    lights_root = top(lights);
+
+    world_rank.assign((size_t)n_tris, -1);
+    if (world_root >= 0) {
+        std::vector<int32_t> leaves;
+        leaves.reserve((size_t)n_tris);
+        walk_ref_leaves(*this, ObjRef{1, world_root}, leaves);
+        for (size_t r = 0; r < leaves.size(); ++r) world_rank[leaves[r]] = (int64_t)r;
+    }
+
+    /* lights: flatten the lights BVH for TraverseSample (BVH.cpp:86-100) */
+    light_order.clear();
+    light_tris.clear();
+    light_nodes.clear();
+    light_root_flat = -1;
+    lights_area = 0.0;
+    if (lights_root >= 0) {
+        std::vector<int32_t> leaves;
+        walk_ref_leaves(*this, ObjRef{1, lights_root}, leaves);
+        std::vector<int32_t> light_index_of_prim((size_t)n_tris, -1);
+        for (size_t i = 0; i < leaves.size(); ++i) {
+            const int32_t p = leaves[i];
+            light_order.push_back(p);
+            light_index_of_prim[p] = (int32_t)i;
+            LightTri L;
+            std::memset(&L, 0, sizeof(L));
+            for (int k = 0; k < 3; ++k) {
+                L.v0[k] = vertices[9 * (size_t)p + k];
+                L.v1[k] = vertices[9 * (size_t)p + 3 + k];
+                L.v2[k] = vertices[9 * (size_t)p + 6 + k];
+                L.normal[k] = shade[p].normal[k];
+            }
+            L.area = area[p];
+            L.material = shade[p].material;
+            L.prim = p;
+            light_tris.push_back(L);
+        }
+        /* nodes reachable from lights_root, renumbered in DFS order */
+        std::vector<int32_t> flat_of((size_t)ref_nodes.size(), -1);
+        std::vector<int32_t> order;
+        std::vector<int32_t> stack{lights_root};
+        while (!stack.empty()) {
+            int32_t c = stack.back();
+            stack.pop_back();
+            if (flat_of[c] >= 0) continue;
+            flat_of[c] = (int32_t)order.size();
+            order.push_back(c);
+            const HostRefNode& n = ref_nodes[c];
+            if (n.right.kind == 1) stack.push_back(n.right.idx);
+            if (n.left.kind == 1) stack.push_back(n.left.idx);
+        }
+        light_nodes.resize(order.size());
+        auto ref_of = [&](ObjRef o) -> int32_t { return o.kind == 1 ? flat_of[o.idx] : ~light_index_of_prim[o.idx]; };
+        for (size_t i = 0; i < order.size(); ++i) {
+            const HostRefNode& n = ref_nodes[order[i]];
+            LightNode ln;
+            ln.left_area = n.left.kind == 0 ? area[n.left.idx] : ref_nodes[n.left.idx].area;
+            ln.left = ref_of(n.left);
+            ln.right = ref_of(n.right);
+            light_nodes[i] = ln;
+        }
+        light_root_flat = 0;
+        lights_area = ref_nodes[lights_root].area;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * SAH BVH2 (binned, top-down), FP32 child boxes rounded outward
+ * ---------------------------------------------------------------------------------------------- */
+namespace {
+
+inline float round_down(double x) {
+    float f = (float)x;
+    if ((double)f > x) f = std::nextafterf(f, -std::numeric_limits<float>::infinity());
+    return f;
+}
+inline float round_up(double x) {
+    float f = (float)x;
+    if ((double)f < x) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+    return f;
+}
+inline double half_area(const Box6& b) {
+    const double dx = b.v[1] - b.v[0], dy = b.v[3] - b.v[2], dz = b.v[5] - b.v[4];
+    return dx * dy + dy * dz + dz * dx;
+}
+inline void box_grow(Box6& a, const Box6& b) {
+    for (int k = 0; k < 3; ++k) {
+        if (b.v[2 * k] < a.v[2 * k]) a.v[2 * k] = b.v[2 * k];
+        if (b.v[2 * k + 1] > a.v[2 * k + 1]) a.v[2 * k + 1] = b.v[2 * k + 1];
+    }
+}
+
+struct TmpNode {
+    Box6 box;
+    int32_t left = -1, right = -1; /* TmpNode indices; -1/-1 = leaf */
+    int32_t first = 0, count = 0;  /* leaf: range in the index array */
+};
+
+struct SahBuilder {
+    const HostScene& s;
+    std::vector<int32_t>& idx;
+    std::vector<TmpNode>& nodes;
+    std::atomic<int32_t>& next;
+    int max_leaf;
+    static constexpr int NB = 16;
+    static constexpr double C_TRI = 1.25, C_NODE = 1.0;
+
+    int32_t alloc() { return next.fetch_add(1); }
+
+    void build(int32_t at, int32_t first, int32_t count, int par_depth) {
+        TmpNode& N = nodes[at];
+        Box6 box = box_empty(), cbox = box_empty();
+        for (int32_t i = first; i < first + count; ++i) {
+            const Box6& b = s.tri_box[idx[i]];
+            box_grow(box, b);
+            for (int k = 0; k < 3; ++k) {
+                const double c = 0.5 * (b.v[2 * k] + b.v[2 * k + 1]);
+                if (c < cbox.v[2 * k]) cbox.v[2 * k] = c;
+                if (c > cbox.v[2 * k + 1]) cbox.v[2 * k + 1] = c;
+            }
+        }
+        N.box = box;
+        N.first = first;
+        N.count = count;
+        if (count == 1) return;
+
+        int best_axis = -1, best_bin = -1;
+        double best_cost = std::numeric_limits<double>::infinity();
+        const double parent_area = half_area(box);
+        for (int axis = 0; axis < 3; ++axis) {
+            const double lo = cbox.v[2 * axis], ext = cbox.v[2 * axis + 1] - lo;
+            if (!(ext > 0.0)) continue;
+            int cnt[NB];
+            Box6 bb[NB];
+            for (int b = 0; b < NB; ++b) { cnt[b] = 0; bb[b] = box_empty(); }
+            const double scale = NB / ext;
+            for (int32_t i = first; i < first + count; ++i) {
+                const Box6& b = s.tri_box[idx[i]];
+                const double c = 0.5 * (b.v[2 * axis] + b.v[2 * axis + 1]);
+                int bin = (int)((c - lo) * scale);
+                if (bin < 0) bin = 0;
+                if (bin >= NB) bin = NB - 1;
+                cnt[bin]++;
+                box_grow(bb[bin], b);
+            }
+            double right_area[NB];
+            int right_cnt[NB];
+            Box6 acc = box_empty();
+            int c = 0;
+            for (int b = NB - 1; b > 0; --b) {
+                box_grow(acc, bb[b]);
+                c += cnt[b];
+                right_area[b] = c ? half_area(acc) : 0.0;
+                right_cnt[b] = c;
+            }
+            acc = box_empty();
+            c = 0;
+            for (int b = 0; b < NB - 1; ++b) {
+                box_grow(acc, bb[b]);
+                c += cnt[b];
+                if (c == 0 || right_cnt[b + 1] == 0) continue;
+                const double cost = half_area(acc) * c + right_area[b + 1] * right_cnt[b + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = b; }
+            }
+        }
+        if (count <= max_leaf) {
+            /* SAH termination: a leaf of `count` triangles against one more node + the split */
+            const double leaf_cost = C_TRI * count;
+            const double split_cost = best_axis >= 0 && parent_area > 0.0 ? C_NODE + C_TRI * best_cost / parent_area
+                                                                          : std::numeric_limits<double>::infinity();
+            if (leaf_cost <= split_cost) return;
+        }
+        int32_t mid;
+        if (best_axis >= 0) {
+            const double lo = cbox.v[2 * best_axis], ext = cbox.v[2 * best_axis + 1] - lo;
+            const double scale = NB / ext;
+            auto it = std::partition(idx.begin() + first, idx.begin() + first + count, [&](int32_t p) {
+                const Box6& b = s.tri_box[p];
+                const double c = 0.5 * (b.v[2 * best_axis] + b.v[2 * best_axis + 1]);
+                int bin = (int)((c - lo) * scale);
+                if (bin < 0) bin = 0;
+                if (bin >= NB) bin = NB - 1;
+                return bin <= best_bin;
+            });
+            mid = (int32_t)(it - idx.begin());
+        } else {
+            mid = first + count / 2; /* coincident centroids: split by position */
+        }
+        if (mid == first || mid == first + count) mid = first + count / 2;
+        const int32_t l = alloc(), r = alloc();
+        nodes[at].left = l;
+        nodes[at].right = r;
+        if (par_depth > 0 && count > 65536) {
+            std::thread t([&, l]() { build(l, first, mid - first, par_depth - 1); });
+            build(r, mid, first + count - mid, par_depth - 1);
+            t.join();
+        } else {
+            build(l, first, mid - first, 0);
+            build(r, mid, first + count - mid, 0);
+        }
+    }
+};
+
+inline void set_child_box(float* lo, float* hi, const Box6& b) {
+    for (int k = 0; k < 3; ++k) { lo[k] = round_down(b.v[2 * k]); hi[k] = round_up(b.v[2 * k + 1]); }
+}
+
+}  // namespace
+
+void HostScene::build_sah_bvh2(int n_threads, int max_leaf) {
+    nodes2.clear();
+    slot_prim.clear();
+    prim_slot.assign((size_t)n_tris, -1);
+    if (max_leaf < 1) max_leaf = 1;
+    if (max_leaf > 8) max_leaf = 8;
+    sah_max_leaf = max_leaf;
+    if (n_tris == 0) return;
+    std::vector<int32_t> idx((size_t)n_tris);
+    for (int64_t i = 0; i < n_tris; ++i) idx[i] = (int32_t)i;
+    std::vector<TmpNode> tmp((size_t)(2 * n_tris + 1));
+    std::atomic<int32_t> next{1};
+    int par = 0;
+    while ((1 << par) < n_threads) ++par;
+    SahBuilder b{*this, idx, tmp, next, max_leaf};
+    b.build(0, 0, (int32_t)n_tris, par + 1);
+
+    /* flatten in DFS preorder; leaves define the slot order */
+    slot_prim.reserve((size_t)n_tris);
+    auto leaf_ref = [&](const TmpNode& n) -> int32_t {
+        const int32_t first_slot = (int32_t)slot_prim.size();
+        for (int32_t i = n.first; i < n.first + n.count; ++i) slot_prim.push_back(idx[i]);
+        return ~((first_slot << 3) | (n.count - 1));
+    };
+    const int32_t NO_CHILD = INT32_MIN;
+    if (tmp[0].left < 0) { /* the whole scene is one leaf: a root with one real child */
+        Node2 root;
+        std::memset(&root, 0, sizeof(root));
+        set_child_box(root.lo0, root.hi0, tmp[0].box);
+        for (int k = 0; k < 3; ++k) { root.lo1[k] = std::numeric_limits<float>::infinity(); root.hi1[k] = -std::numeric_limits<float>::infinity(); }
+        root.child0 = leaf_ref(tmp[0]);
+        root.child1 = NO_CHILD;
+        nodes2.push_back(root);
+    } else {
+        struct Work { int32_t tmp_idx, flat_idx; };
+        std::vector<Work> stack;
+        nodes2.emplace_back();
+        stack.push_back({0, 0});
+        while (!stack.empty()) {
+            Work w = stack.back();
+            stack.pop_back();
+            const TmpNode& n = tmp[w.tmp_idx];
+            const TmpNode& L = tmp[n.left];
+            const TmpNode& R = tmp[n.right];
+            Node2 out;
+            std::memset(&out, 0, sizeof(out));
+            set_child_box(out.lo0, out.hi0, L.box);
+            set_child_box(out.lo1, out.hi1, R.box);
+            /* left subtree first so that its nodes and slots directly follow the parent */
+            int32_t c0, c1;
+            if (L.left < 0) c0 = leaf_ref(L);
+            else { c0 = (int32_t)nodes2.size(); nodes2.emplace_back(); }
+            if (R.left < 0) c1 = leaf_ref(R);
+            else { c1 = (int32_t)nodes2.size(); nodes2.emplace_back(); }
+            out.child0 = c0;
+            out.child1 = c1;
+            nodes2[w.flat_idx] = out;
+            if (R.left >= 0) stack.push_back({n.right, c1});
+            if (L.left >= 0) stack.push_back({n.left, c0});
+        }
+    }
+    for (size_t sidx = 0; sidx < slot_prim.size(); ++sidx) prim_slot[slot_prim[sidx]] = (int32_t)sidx;
+    isect_slots.resize((size_t)n_tris);
+    for (int64_t sidx = 0; sidx < n_tris; ++sidx) isect_slots[sidx] = isect[slot_prim[sidx]];
+}
+
+void HostScene::use_reference_slots() {
+    nodes2.clear();
+    slot_prim.assign((size_t)n_tris, 0);
+    prim_slot.assign((size_t)n_tris, -1);
+    for (int64_t p = 0; p < n_tris; ++p) {
+        const int64_t r = world_rank[p];
+        slot_prim[(size_t)r] = (int32_t)p;
+        prim_slot[(size_t)p] = (int32_t)r;
+    }
+    isect_slots.resize((size_t)n_tris);
+    for (int64_t sidx = 0; sidx < n_tris; ++sidx) isect_slots[sidx] = isect[slot_prim[sidx]];
+}
+
+/* reference world BVH -> RefNode[], nodes renumbered in DFS order, triangle leaves = ~slot */
+void HostScene::flatten_reference_world() {
+    ref_flat.clear();
+    ref_root_flat = -1;
+    if (world_root < 0) return;
+    std::vector<int32_t> flat_of((size_t)ref_nodes.size(), -1);
+    std::vector<int32_t> order;
+    std::vector<int32_t> stack{world_root};
+    while (!stack.empty()) {
+        int32_t c = stack.back();
+        stack.pop_back();
+        if (flat_of[c] >= 0) continue;
+        flat_of[c] = (int32_t)order.size();
+        order.push_back(c);
+        const HostRefNode& n = ref_nodes[c];
+        if (n.right.kind == 1) stack.push_back(n.right.idx);
+        if (n.left.kind == 1) stack.push_back(n.left.idx);
+    }
+    ref_flat.resize(order.size());
+    auto ref_of = [&](ObjRef o) -> int32_t { return o.kind == 1 ? flat_of[o.idx] : ~prim_slot[o.idx]; };
+    for (size_t i = 0; i < order.size(); ++i) {
+        const HostRefNode& n = ref_nodes[order[i]];
+        RefNode out;
+        std::memset(&out, 0, sizeof(out));
+        for (int k = 0; k < 6; ++k) out.box[k] = n.box.v[k];
+        out.left = ref_of(n.left);
+        out.right = ref_of(n.right);
+        ref_flat[i] = out;
+    }
+    ref_root_flat = 0;
+}
+
+}  // namespace prt

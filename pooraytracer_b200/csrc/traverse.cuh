@@ -1,0 +1,217 @@
+/*
+ * traverse.cuh — ray / box, ray / triangle and the two BVH walks (device code).
+ *
+ *   tri_test        Triangle::Hit + IsInterior      Source/Triangle.cpp:54-83,100-113
+ *   slab_f64        AABB::Hit                       Source/AABB.cpp:38-64
+ *   trace_reference BVHNode::Hit                    Source/BVH.cpp:51-61 (the reference's own tree
+ *                                                   in the reference's own order: bit-exact)
+ *   trace_bvh2      same hits through the SAH BVH2 with near-first ordering; equal-t candidates
+ *                   (the only case in which visiting order matters: Interval::Contains is
+ *                   inclusive, Source/Interval.h:21-23, so a later candidate with the same t
+ *                   overwrites an earlier one, Source/BVH.cpp:58) are re-resolved by
+ *                   trace_reference.
+ *
+ * All arithmetic is FP64 in the reference's operation order; the file is compiled with
+ * -fmad=false so nothing is contracted into an FMA (the reference objects contain none).
+ */
+#ifndef PRT_TRAVERSE_CUH
+#define PRT_TRAVERSE_CUH
+
+#include "device_scene.h"
+#include "prt_math.h"
+
+namespace prt {
+
+#define PRT_STACK 64
+#define PRT_NO_CHILD INT32_MIN
+
+struct Hit {
+    int32_t slot; /* -1: miss */
+    double t, alpha, beta;
+};
+
+/* node / triangle records fetched; only maintained by the COUNT instantiations
+ * (PRT_RENDER_COUNTERS / prt_set_counters), which feed the roofline's algorithmic bytes */
+struct VisitCounters {
+    unsigned long long nodes, tris;
+};
+#define PRT_COUNT_NODE(c) do { if (COUNT) (c).nodes++; } while (0)
+#define PRT_COUNT_TRI(c) do { if (COUNT) (c).tris++; } while (0)
+
+/* Triangle::Hit. The 128-byte record is read as 2 + 6 128-bit loads: the plane first, the rest
+ * only for candidates whose t is inside the interval. */
+__device__ __forceinline__ bool tri_test(const TriIsect* __restrict__ T, d3 o, d3 d, double tmin, double tmax,
+                                         double& t_out, double& alpha_out, double& beta_out) {
+    const double2* __restrict__ p = reinterpret_cast<const double2*>(T);
+    const double2 q0 = __ldg(p), q1 = __ldg(p + 1); /* n.x n.y | n.z D */
+    const d3 n = mk3(q0.x, q0.y, q1.x);
+    const double denom = dot(n, d);
+    if (fabs(denom) < 1e-8) return false;
+    const double t = (q1.y - dot(n, o)) / denom;
+    if (!(tmin <= t && t <= tmax)) return false; /* Interval::Contains, inclusive */
+    const double2 q2 = __ldg(p + 2), q3 = __ldg(p + 3), q4 = __ldg(p + 4), q5 = __ldg(p + 5), q6 = __ldg(p + 6), q7 = __ldg(p + 7);
+    const d3 w = mk3(q2.x, q2.y, q3.x);
+    const d3 v0 = mk3(q3.y, q4.x, q4.y);
+    const d3 e0 = mk3(q5.x, q5.y, q6.x);
+    const d3 e1 = mk3(q6.y, q7.x, q7.y);
+    const d3 pt = o + d * t; /* Ray.h:13 */
+    const d3 v0p = pt - v0;
+    const double alpha = dot(w, cross(v0p, e1));
+    const double beta = dot(w, cross(e0, v0p));
+    if (alpha != alpha || beta != beta) return false;
+    if ((alpha < 0) || (beta < 0) || (alpha + beta > 1)) return false;
+    t_out = t;
+    alpha_out = alpha;
+    beta_out = beta;
+    return true;
+}
+
+/* AABB::Hit on one axis: the reference's ordered shrink (NaNs fall into the else branch and change
+ * nothing). inv = 1.0 / d[i] is hoisted out of the node loop: same operands, same quotient. */
+__device__ __forceinline__ void slab_axis(double bmin, double bmax, double o, double inv, double& lo, double& hi) {
+    const double t0 = (bmin - o) * inv;
+    const double t1 = (bmax - o) * inv;
+    if (t0 < t1) {
+        if (t0 > lo) lo = t0;
+        if (t1 < hi) hi = t1;
+    } else {
+        if (t1 > lo) lo = t1;
+        if (t0 < hi) hi = t0;
+    }
+}
+
+/* The reference's BVH in the reference's order. Later candidates with equal t overwrite. */
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ void trace_reference(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, VisitCounters& cnt) {
+    hit.slot = -1;
+    hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
+    if (S.ref_root < 0) return;
+    const d3 inv = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
+    int32_t stack[PRT_STACK];
+    int sp = 0;
+    int32_t cur = S.ref_root;
+    double tbest = tmax;
+    for (;;) {
+        if (cur >= 0) {
+            const double2* __restrict__ p = reinterpret_cast<const double2*>(S.ref_nodes + cur);
+            const double2 bx = __ldg(p), by = __ldg(p + 1), bz = __ldg(p + 2);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
+            PRT_COUNT_NODE(cnt);
+            double lo = tmin, hi = tbest;
+            bool ok = true;
+            slab_axis(bx.x, bx.y, o.x, inv.x, lo, hi);
+            if (hi <= lo) ok = false;
+            if (ok) { slab_axis(by.x, by.y, o.y, inv.y, lo, hi); if (hi <= lo) ok = false; }
+            if (ok) { slab_axis(bz.x, bz.y, o.z, inv.z, lo, hi); if (hi <= lo) ok = false; }
+            if (ok) {
+                /* left, then right (BVH.cpp:57-58); a span-1 node has left == right (BVH.cpp:21-24)
+                 * and testing the same object again with max = its own t changes nothing */
+                if (ch.y != ch.x && sp < PRT_STACK) stack[sp++] = ch.y;
+                cur = ch.x;
+                continue;
+            }
+        } else {
+            const int32_t slot = ~cur;
+            double t, a, b;
+            PRT_COUNT_TRI(cnt);
+            if (tri_test(S.tris + slot, o, d, tmin, tbest, t, a, b)) {
+                hit.slot = slot; hit.t = t; hit.alpha = a; hit.beta = b;
+                tbest = t;
+                if (ANY) return;
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+}
+
+/* One child box of a Node2 against the ray: FP32 bounds (rounded outward on the host) widened to
+ * FP64 and run through the reference's slab formula. Rounding is monotone, so a box that contains
+ * the reference's box yields an interval that contains the reference's interval: nothing the
+ * reference would have visited is culled. Returns the entry distance through `entry`. */
+__device__ __forceinline__ bool child_box(float lx, float ly, float lz, float hx, float hy, float hz, d3 o, d3 inv, double tmin,
+                                          double tbest, double& entry) {
+    double lo = tmin, hi = tbest;
+    slab_axis((double)lx, (double)hx, o.x, inv.x, lo, hi);
+    slab_axis((double)ly, (double)hy, o.y, inv.y, lo, hi);
+    slab_axis((double)lz, (double)hz, o.z, inv.z, lo, hi);
+    entry = lo;
+    return !(hi <= lo);
+}
+
+/* SAH BVH2, near child first. `tie` is set when two different triangles were accepted with the
+ * very same t: the caller then asks trace_reference which one the reference reports. */
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, bool& tie, VisitCounters& cnt) {
+    hit.slot = -1;
+    hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
+    tie = false;
+    if (S.n_tris == 0) return;
+    const d3 inv = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
+    int32_t stack[PRT_STACK];
+    int sp = 0;
+    int32_t cur = 0;
+    double tbest = tmax;
+    for (;;) {
+        if (cur >= 0) {
+            const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes2 + cur);
+            const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+            const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
+            PRT_COUNT_NODE(cnt);
+            /* a = lo0.xyz hi0.x | b = hi0.yz lo1.xy | c = lo1.z hi1.xyz */
+            double e0, e1;
+            const bool h0 = child_box(a.x, a.y, a.z, a.w, b.x, b.y, o, inv, tmin, tbest, e0);
+            const bool h1 = child_box(b.z, b.w, c.x, c.y, c.z, c.w, o, inv, tmin, tbest, e1) && ch.y != PRT_NO_CHILD;
+            if (h0 && h1) {
+                const bool swap = e1 < e0;
+                const int32_t near_c = swap ? ch.y : ch.x, far_c = swap ? ch.x : ch.y;
+                if (sp < PRT_STACK) stack[sp++] = far_c;
+                cur = near_c;
+                continue;
+            }
+            if (h0) { cur = ch.x; continue; }
+            if (h1) { cur = ch.y; continue; }
+        } else {
+            const int32_t code = ~cur;
+            const int32_t first = code >> 3, count = (code & 7) + 1;
+            for (int32_t i = 0; i < count; ++i) {
+                double t, al, be;
+                PRT_COUNT_TRI(cnt);
+                if (tri_test(S.tris + first + i, o, d, tmin, tbest, t, al, be)) {
+                    if (ANY) { hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be; return; }
+                    if (hit.slot >= 0 && t == tbest) tie = true;
+                    hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
+                    tbest = t;
+                }
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+}
+
+/* closest hit through whichever structure is committed; result identical to the reference's */
+template <bool COUNT>
+__device__ __forceinline__ void closest_hit(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, VisitCounters& cnt) {
+    if (S.nodes2) {
+        bool tie;
+        trace_bvh2<false, COUNT>(S, o, d, tmin, tmax, hit, tie, cnt);
+        if (tie) trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+    } else {
+        trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+    }
+}
+template <bool COUNT>
+__device__ __forceinline__ bool any_hit(const DevScene& S, d3 o, d3 d, double tmin, double tmax, VisitCounters& cnt) {
+    Hit hit;
+    if (S.nodes2) {
+        bool tie;
+        trace_bvh2<true, COUNT>(S, o, d, tmin, tmax, hit, tie, cnt);
+    } else {
+        trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+    }
+    return hit.slot >= 0;
+}
+
+}  // namespace prt
+#endif

@@ -1,0 +1,82 @@
+"""Generates tests/golden/*.npz by running the inputs of tests/cases.py through the UNMODIFIED
+reference sources (oracle/_ref/libprt_ref.so, built from /root/reference by oracle/Makefile).
+
+Run in the build container only (needs /root/reference):   python tests/golden/make_golden.py
+The fixtures pin the oracle port (tests/test_oracle_pinning.py) and, on the GPU box where the
+reference cannot be built, stand in for it.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import cases  # noqa: E402
+import oracle_lib as ol  # noqa: E402
+from pooraytracer_b200.api import make_camera, make_params  # noqa: E402
+
+
+def main():
+    assert ol.available("ref"), "build oracle/_ref first (make -C oracle ref)"
+    tag = ol.PER_TRIANGLE_MATERIAL | ol.UV_TAG
+    for key, make in list(cases.SCENES.items()) + [("ties", cases.tie_scene)]:
+        sc = make()
+        R = ol.OracleScene("ref", sc, tag)
+        o, d = cases.tie_rays() if key == "ties" else cases.ray_batch(sc)
+        prim, t, a, b = R.trace_closest(o, d, 1e-4, np.inf)
+        rank, lo = R.reference_order()
+        out = dict(prim=prim, t=t, alpha=a, beta=b, world_rank=rank, light_order=lo)
+        # bounded interval (the shadow-ray style query)
+        tmax = np.where(prim >= 0, t, 1.0) * np.where(np.arange(len(t)) % 3 == 0, 1.0, 0.5 + (np.arange(len(t)) % 7) * 0.25)
+        p2, t2, _, _ = R.trace_closest(o, d, 1e-3, tmax)
+        out.update(tmax=tmax, prim_bounded=p2, t_bounded=t2)
+        recs = np.stack([R.triangle_record(p) for p in range(0, sc.n_triangles, max(1, sc.n_triangles // 64))])
+        out["tri_records"] = recs
+        if len(lo):
+            lo_o, lo_u = cases.light_inputs(sc)
+            pos, nrm, front, pdf, lprim = R.sample_lights(lo_o, lo_u)
+            out.update(l_pos=pos, l_nrm=nrm, l_front=front, l_pdf=pdf, l_prim=lprim)
+        np.savez_compressed(os.path.join(HERE, f"rays_{key}.npz"), **out)
+        print("rays", key, len(prim), int((prim >= 0).sum()), "hits")
+        R.close()
+
+    # materials + textures on the tiny scene (every material type, one texture of each channel count
+    # lives in the bathroom scene)
+    sc = cases.tiny()
+    for flags, name in ((0, "raw"), (ol.DEFINE_UB, "defined")):
+        R = ol.OracleScene("ref", sc, flags)
+        rows = []
+        for mi in range(len(sc.materials)):
+            for (rd, nrm, tng, uv, u) in cases.scatter_inputs():
+                att, od, nd, ok = R.material_scatter(mi, rd, nrm, tng, uv, u)
+                rows.append(np.concatenate([[mi], att, od, [nd, float(ok)]]))
+        np.savez_compressed(os.path.join(HERE, f"scatter_tiny_{name}.npz"), rows=np.array(rows))
+        R.close()
+    scb = cases.bathroom_small()
+    R = ol.OracleScene("ref", scb, 0)
+    uv = np.concatenate([cases.hash_uniform(800, 12, 1).reshape(-1, 2) * 1.4 - 0.2,
+                         np.array([[0, 0], [1, 1], [0, 1], [1, 0], [0.5, 0.5], [1.0, 0.999999], [-3, 7]], dtype=np.float64)])
+    tex = {f"tex{i}": R.texture_value(i, uv) for i in range(len(scb.textures))}
+    np.savez_compressed(os.path.join(HERE, "texture_bathroom.npz"), uv=uv, **tex)
+    R.close()
+
+    for name, (key, w, h, spp, depth, nee, rkey, bg) in cases.RENDER_CASES.items():
+        sc = cases.SCENES[key]()
+        R = ol.OracleScene("ref", sc, ol.DEFINE_UB)
+        cam = make_camera(sc.camera, w, h)
+        prm = make_params(spp, depth, sample_lights=nee, rng_key=rkey, background=bg)
+        img, info = R.render(cam, prm, ol.RNG_COUNTER, nthreads=8)
+        px = [(w // 2, h // 2), (3, 5), (w - 2, h - 3), (w // 3, 2 * h // 3)]
+        samples = np.stack([R.pixel_samples(cam, prm, x, y) for x, y in px])
+        np.savez_compressed(os.path.join(HERE, f"render_{name}.npz"), image=img, pixels=np.array(px), samples=samples,
+                            world_hit_calls=info.world_hit_calls, shadow_calls=info.shadow_calls)
+        print("render", name, img.shape, float(img.mean()), info.world_hit_calls)
+        R.close()
+
+
+if __name__ == "__main__":
+    main()
