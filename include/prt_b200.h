@@ -127,6 +127,9 @@ typedef struct prt_camera {
                                           of Source/Camera.cpp:150-155 instead of any-hit over
                                           [1e-3, dist-1e-3] (equivalent up to rounding)          */
 #define PRT_RENDER_COUNTERS 2u         /* count BVH node / triangle visits (prt_get_stats)       */
+#define PRT_RENDER_STAGE_TIMING 4u     /* CUDA events around the extend / shade / shadow kernels of
+                                          every bounce (prt_stats.extend_ms ...); the call then
+                                          waits for each pass                                     */
 
 typedef struct prt_render_params {
     int32_t samples_per_pixel; /* total spp: pixelSamplesScale = 1/spp (Source/Camera.cpp:83)    */

@@ -28,6 +28,7 @@ ACCEL_SAH_BVH2 = 1
 
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
+RENDER_STAGE_TIMING = 4
 
 c_double3 = C.c_double * 3
 

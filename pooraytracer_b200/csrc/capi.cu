@@ -112,6 +112,7 @@ struct prt_scene {
     int64_t pool_cap = 0;
     int pool_bounces = 0;
 
+    std::vector<cudaEvent_t> stage_events;
     bool count_visits = false;
     prt_stats stats;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -121,6 +122,7 @@ struct prt_scene {
     ~prt_scene() {
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
+        for (cudaEvent_t e : stage_events) cudaEventDestroy(e);
     }
 };
 
@@ -140,6 +142,7 @@ LaunchConfig launch_config(const prt_context* ctx) {
     lc.sm_count = ctx->sm_count;
     const char* env = std::getenv("PRT_BLOCKS_PER_SM");
     lc.trace_blocks_per_sm = env ? std::max(1, std::atoi(env)) : 8;
+    lc.stage_events = nullptr;
     return lc;
 }
 
@@ -536,7 +539,17 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
     PathBuffers pb = path_buffers(s);
     pb.counters = counting ? s->d_counters.p : nullptr;
-    const LaunchConfig lc = launch_config(s->ctx);
+    LaunchConfig lc = launch_config(s->ctx);
+    const bool stage_timing = (rcn.flags & PRT_RENDER_STAGE_TIMING) != 0;
+    if (stage_timing) {
+        while (s->stage_events.size() < (size_t)4 * n_bounces) {
+            cudaEvent_t e;
+            CUDA_TRY(cudaEventCreate(&e));
+            s->stage_events.push_back(e);
+        }
+        lc.stage_events = s->stage_events.data();
+    }
+    double extend_ms = 0.0, shade_ms = 0.0, shadow_ms = 0.0;
     uint64_t launches = 0;
     CUDA_TRY(cudaEventRecord(s->ev0, st));
     for (int s0 = sb; s0 < se; s0 += per_pass) {
@@ -545,7 +558,20 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
         rcn.n_paths = rcn.n_samples * rcn.npix;
         launches += (uint64_t)launch_render_pass(s->dev, s->d_prim_class.p, rcn, pb, rgb_device, s->d_counters.p, lc, st);
         CUDA_TRY(cudaGetLastError());
+        if (stage_timing) {
+            CUDA_TRY(cudaStreamSynchronize(st));
+            for (int b = 0; b < n_bounces; ++b) {
+                float a = 0.f, c = 0.f, d = 0.f;
+                cudaEventElapsedTime(&a, lc.stage_events[4 * b], lc.stage_events[4 * b + 1]);
+                cudaEventElapsedTime(&c, lc.stage_events[4 * b + 1], lc.stage_events[4 * b + 2]);
+                cudaEventElapsedTime(&d, lc.stage_events[4 * b + 2], lc.stage_events[4 * b + 3]);
+                extend_ms += a; shade_ms += c; shadow_ms += d;
+            }
+        }
     }
+    s->stats.extend_ms = extend_ms;
+    s->stats.shade_ms = shade_ms;
+    s->stats.shadow_ms = shadow_ms;
     CUDA_TRY(cudaEventRecord(s->ev1, st));
     s->timing_pending = true;
     s->rays_pending = true;

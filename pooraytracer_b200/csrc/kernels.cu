@@ -409,18 +409,23 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int grid_paths = (int)(want < persistent ? want : persistent);
     k_raygen<<<(int)(((int64_t)rc.n_paths + 255) / 256 < lc.sm_count * 8 ? ((int64_t)rc.n_paths + 255) / 256 : lc.sm_count * 8), 256, 0, st>>>(rc, pb);
     ++launches;
+    cudaEvent_t* ev = lc.stage_events;
     for (int b = 0; b < n_bounces; ++b) {
+        if (ev) cudaEventRecord(ev[4 * b], st);
         if (count) k_extend<true><<<grid_paths, 128, 0, st>>>(S, prim_class, rc, pb, b);
         else k_extend<false><<<grid_paths, 128, 0, st>>>(S, prim_class, rc, pb, b);
+        if (ev) cudaEventRecord(ev[4 * b + 1], st);
         k_shade<CLS_LAMBERT><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
         k_shade<CLS_PHONG><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
         k_shade<CLS_MIRROR><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
         launches += 4;
+        if (ev) cudaEventRecord(ev[4 * b + 2], st);
         if (rc.sample_lights) {
             if (count) k_shadow<true><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
             else k_shadow<false><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
             ++launches;
         }
+        if (ev) cudaEventRecord(ev[4 * b + 3], st);
     }
     k_accumulate<<<(rc.npix + 255) / 256 < lc.sm_count * 8 ? (rc.npix + 255) / 256 : lc.sm_count * 8, 256, 0, st>>>(rc, pb, rgb);
     k_pass_stats<<<1, 32, 0, st>>>(pb.ctrl, n_bounces, rc.n_paths, totals);

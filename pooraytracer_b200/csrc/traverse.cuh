@@ -5,10 +5,10 @@
  *   slab_f64        AABB::Hit                       Source/AABB.cpp:38-64
  *   trace_reference BVHNode::Hit                    Source/BVH.cpp:51-61 (the reference's own tree
  *                                                   in the reference's own order: bit-exact)
- *   trace_bvh2      same hits through the SAH BVH2 with near-first ordering; equal-t candidates
- *                   (the only case in which visiting order matters: Interval::Contains is
- *                   inclusive, Source/Interval.h:21-23, so a later candidate with the same t
- *                   overwrites an earlier one, Source/BVH.cpp:58) are re-resolved by
+ *   trace_bvh2      same hits through the SAH BVH2 with near-first ordering; hits on a triangle's
+ *                   boundary (the only place where the reference's own tree can matter: equal-t
+ *                   candidates, Source/Interval.h:21-23 + Source/BVH.cpp:58, and its box test's
+ *                   rejection of degenerate intervals, Source/AABB.cpp:62) are re-resolved by
  *                   trace_reference.
  *
  * All arithmetic is FP64 in the reference's operation order; the file is compiled with
@@ -139,13 +139,26 @@ __device__ __forceinline__ bool child_box(float lx, float ly, float lz, float hx
     return !(hi <= lo);
 }
 
-/* SAH BVH2, near child first. `tie` is set when two different triangles were accepted with the
- * very same t: the caller then asks trace_reference which one the reference reports. */
+/* A hit within PRT_EDGE_EPS (barycentric units) of the triangle's boundary. Only there can the
+ * reference's answer depend on its own tree: (a) its box test rejects a degenerate interval
+ * (`t.max <= t.min`, AABB.cpp:62), which happens for a ray that enters a leaf / ancestor box exactly
+ * where it meets the triangle — boxes touch their triangles only at vertices and edges; (b) two
+ * triangles sharing that edge / vertex are met at the very same t and the later one in the
+ * reference's visiting order wins (Interval.h:21-23, BVH.cpp:58). Rounding decides those cases
+ * within ~1e-12 of the boundary; the margin is four orders wider. */
+#define PRT_EDGE_EPS 1e-7
+__device__ __forceinline__ bool on_boundary(double alpha, double beta) {
+    return alpha < PRT_EDGE_EPS || beta < PRT_EDGE_EPS || 1.0 - (alpha + beta) < PRT_EDGE_EPS;
+}
+
+/* SAH BVH2, near child first. `recheck` is set when the answer could depend on the reference's own
+ * tree (see on_boundary): the caller then asks trace_reference. Everything else is decided here:
+ * the triangle arithmetic is the reference's, and the boxes only ever contain the reference's. */
 template <bool ANY, bool COUNT>
-__device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, bool& tie, VisitCounters& cnt) {
+__device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, bool& recheck, VisitCounters& cnt) {
     hit.slot = -1;
     hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
-    tie = false;
+    recheck = false;
     if (S.n_tris == 0) return;
     const d3 inv = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
     int32_t stack[PRT_STACK];
@@ -178,8 +191,14 @@ __device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double
                 double t, al, be;
                 PRT_COUNT_TRI(cnt);
                 if (tri_test(S.tris + first + i, o, d, tmin, tbest, t, al, be)) {
-                    if (ANY) { hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be; return; }
-                    if (hit.slot >= 0 && t == tbest) tie = true;
+                    if (ANY) {
+                        /* a boundary hit may be one the reference's boxes reject: keep looking for
+                         * an interior one, and let the reference decide if none turns up */
+                        if (on_boundary(al, be)) { recheck = true; continue; }
+                        hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
+                        recheck = false;
+                        return;
+                    }
                     hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
                     tbest = t;
                 }
@@ -188,15 +207,16 @@ __device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double
         if (sp == 0) break;
         cur = stack[--sp];
     }
+    if (!ANY && hit.slot >= 0) recheck = on_boundary(hit.alpha, hit.beta);
 }
 
 /* closest hit through whichever structure is committed; result identical to the reference's */
 template <bool COUNT>
 __device__ __forceinline__ void closest_hit(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, VisitCounters& cnt) {
     if (S.nodes2) {
-        bool tie;
-        trace_bvh2<false, COUNT>(S, o, d, tmin, tmax, hit, tie, cnt);
-        if (tie) trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+        bool recheck;
+        trace_bvh2<false, COUNT>(S, o, d, tmin, tmax, hit, recheck, cnt);
+        if (recheck) trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
     } else {
         trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
     }
@@ -205,8 +225,9 @@ template <bool COUNT>
 __device__ __forceinline__ bool any_hit(const DevScene& S, d3 o, d3 d, double tmin, double tmax, VisitCounters& cnt) {
     Hit hit;
     if (S.nodes2) {
-        bool tie;
-        trace_bvh2<true, COUNT>(S, o, d, tmin, tmax, hit, tie, cnt);
+        bool recheck;
+        trace_bvh2<true, COUNT>(S, o, d, tmin, tmax, hit, recheck, cnt);
+        if (recheck) trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
     } else {
         trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
     }
