@@ -128,13 +128,28 @@ __device__ __forceinline__ void trace_reference(const DevScene& S, d3 o, d3 d, d
 /* One child box of a Node2 against the ray: FP32 bounds (rounded outward on the host) widened to
  * FP64 and run through the reference's slab formula. Rounding is monotone, so a box that contains
  * the reference's box yields an interval that contains the reference's interval: nothing the
- * reference would have visited is culled. Returns the entry distance through `entry`. */
+ * reference would have visited is culled. The one exception is the NaN of 0 * inf (a ray with a
+ * zero direction component lying exactly in a face plane of the box), where the reference's ordered
+ * shrink empties the interval; here such an axis puts no constraint on t (the ray is inside the
+ * closed slab), and hits the reference would have lost that way lie on a triangle's boundary, which
+ * is re-resolved through the reference's own tree anyway. Returns the entry distance. */
+__device__ __forceinline__ void slab_axis_conservative(double bmin, double bmax, double o, double inv, double& lo, double& hi) {
+    const double t0 = (bmin - o) * inv;
+    const double t1 = (bmax - o) * inv;
+    if (t0 < t1) {
+        if (t0 > lo) lo = t0;
+        if (t1 < hi) hi = t1;
+    } else if (t0 >= t1) { /* false for NaN: no constraint */
+        if (t1 > lo) lo = t1;
+        if (t0 < hi) hi = t0;
+    }
+}
 __device__ __forceinline__ bool child_box(float lx, float ly, float lz, float hx, float hy, float hz, d3 o, d3 inv, double tmin,
                                           double tbest, double& entry) {
     double lo = tmin, hi = tbest;
-    slab_axis((double)lx, (double)hx, o.x, inv.x, lo, hi);
-    slab_axis((double)ly, (double)hy, o.y, inv.y, lo, hi);
-    slab_axis((double)lz, (double)hz, o.z, inv.z, lo, hi);
+    slab_axis_conservative((double)lx, (double)hx, o.x, inv.x, lo, hi);
+    slab_axis_conservative((double)ly, (double)hy, o.y, inv.y, lo, hi);
+    slab_axis_conservative((double)lz, (double)hz, o.z, inv.z, lo, hi);
     entry = lo;
     return !(hi <= lo);
 }
@@ -199,6 +214,9 @@ __device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double
                         recheck = false;
                         return;
                     }
+                    /* two different triangles at the very same t (coplanar overlap, shared edge):
+                     * the reference's visiting order decides */
+                    recheck = hit.slot >= 0 && t == tbest;
                     hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
                     tbest = t;
                 }
@@ -207,7 +225,7 @@ __device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double
         if (sp == 0) break;
         cur = stack[--sp];
     }
-    if (!ANY && hit.slot >= 0) recheck = on_boundary(hit.alpha, hit.beta);
+    if (!ANY && hit.slot >= 0 && on_boundary(hit.alpha, hit.beta)) recheck = true;
 }
 
 /* closest hit through whichever structure is committed; result identical to the reference's */
