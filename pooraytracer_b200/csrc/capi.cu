@@ -105,9 +105,8 @@ struct prt_scene {
     DevBuf<float> s_rgb32f;
 
     /* wavefront pool */
-    DevBuf<double> p_ray, p_T, p_L, p_hit, p_shadow;
-    DevBuf<int32_t> p_hit_prim, p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qs;
-    DevBuf<uint32_t> p_dim, p_flags;
+    DevBuf<PathRec> p_rec;
+    DevBuf<int32_t> p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qs;
     DevBuf<BounceCtrl> p_ctrl;
     int64_t pool_cap = 0;
     int pool_bounces = 0;
@@ -155,20 +154,13 @@ int64_t pass_path_budget() {
 
 int ensure_pool(prt_scene* s, int64_t cap, int n_bounces) {
     if (cap > s->pool_cap) {
-        CUDA_TRY(s->p_ray.ensure((size_t)cap * 6));
-        CUDA_TRY(s->p_T.ensure((size_t)cap * 3));
-        CUDA_TRY(s->p_L.ensure((size_t)cap * 3));
-        CUDA_TRY(s->p_hit.ensure((size_t)cap * 3));
-        CUDA_TRY(s->p_shadow.ensure((size_t)cap * 7));
-        CUDA_TRY(s->p_hit_prim.ensure((size_t)cap));
+        CUDA_TRY(s->p_rec.ensure((size_t)cap));
         CUDA_TRY(s->p_q0.ensure((size_t)cap));
         CUDA_TRY(s->p_q1.ensure((size_t)cap));
         CUDA_TRY(s->p_qm0.ensure((size_t)cap));
         CUDA_TRY(s->p_qm1.ensure((size_t)cap));
         CUDA_TRY(s->p_qm2.ensure((size_t)cap));
         CUDA_TRY(s->p_qs.ensure((size_t)cap));
-        CUDA_TRY(s->p_dim.ensure((size_t)cap));
-        CUDA_TRY(s->p_flags.ensure((size_t)cap));
         s->pool_cap = cap;
     }
     if (n_bounces + 2 > s->pool_bounces) {
@@ -181,8 +173,7 @@ int ensure_pool(prt_scene* s, int64_t cap, int n_bounces) {
 PathBuffers path_buffers(prt_scene* s) {
     PathBuffers pb;
     pb.cap = s->pool_cap;
-    pb.ray = s->p_ray.p; pb.T = s->p_T.p; pb.L = s->p_L.p; pb.hit = s->p_hit.p;
-    pb.hit_prim = s->p_hit_prim.p; pb.shadow = s->p_shadow.p; pb.dim = s->p_dim.p; pb.flags = s->p_flags.p;
+    pb.rec = s->p_rec.p;
     pb.q_extend[0] = s->p_q0.p; pb.q_extend[1] = s->p_q1.p;
     pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p;
     pb.q_shadow = s->p_qs.p;

@@ -28,6 +28,7 @@
 #include "rng.cuh"
 #include "shading.cuh"
 #include "traverse.cuh"
+#include "traverse_warp.cuh"
 
 namespace prt {
 
@@ -70,25 +71,49 @@ __device__ __forceinline__ void flush_counters(const VisitCounters& c, unsigned 
 /* ------------------------------------------------------------------------------------------------
  * ray queries
  * ---------------------------------------------------------------------------------------------- */
+struct ClosestQueryPolicy {
+    const double *o, *d, *tmin, *tmax;
+    int32_t* prim;
+    double *t, *alpha, *beta;
+    const int32_t* slot_prim;
+    __device__ __forceinline__ bool load(int32_t i, d3& ro, d3& rd, double& t0, double& t1) const {
+        ro = mk3(o[3 * (int64_t)i], o[3 * (int64_t)i + 1], o[3 * (int64_t)i + 2]);
+        rd = mk3(d[3 * (int64_t)i], d[3 * (int64_t)i + 1], d[3 * (int64_t)i + 2]);
+        t0 = tmin[i];
+        t1 = tmax[i];
+        return true;
+    }
+    __device__ __forceinline__ void retire(bool finished, int32_t i, const Hit& h) const {
+        if (!finished) return;
+        prim[i] = h.slot >= 0 ? slot_prim[h.slot] : -1;
+        if (t) t[i] = h.t;
+        if (alpha) alpha[i] = h.alpha;
+        if (beta) beta[i] = h.beta;
+    }
+};
+struct AnyQueryPolicy {
+    const double *o, *d, *tmin, *tmax;
+    uint8_t* hit;
+    __device__ __forceinline__ bool load(int32_t i, d3& ro, d3& rd, double& t0, double& t1) const {
+        ro = mk3(o[3 * (int64_t)i], o[3 * (int64_t)i + 1], o[3 * (int64_t)i + 2]);
+        rd = mk3(d[3 * (int64_t)i], d[3 * (int64_t)i + 1], d[3 * (int64_t)i + 2]);
+        t0 = tmin[i];
+        t1 = tmax[i];
+        return true;
+    }
+    __device__ __forceinline__ void retire(bool finished, int32_t i, const Hit& h) const {
+        if (finished) hit[i] = h.slot >= 0 ? 1 : 0;
+    }
+};
+
 template <bool COUNT>
 __global__ void __launch_bounds__(128) k_trace_closest(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                        const double* __restrict__ tmin, const double* __restrict__ tmax,
                                                        int32_t* __restrict__ prim, double* __restrict__ t, double* __restrict__ alpha,
                                                        double* __restrict__ beta, int32_t* fetch, unsigned long long* counters) {
     VisitCounters cnt = {0, 0};
-    for (;;) {
-        const int64_t i = (int64_t)warp_fetch(fetch) + lane_id();
-        if (i - lane_id() >= n) break;
-        if (i < n) {
-            Hit h;
-            closest_hit<COUNT>(S, mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), tmin[i], tmax[i], h, cnt);
-            prim[i] = h.slot >= 0 ? S.slot_prim[h.slot] : -1;
-            if (t) t[i] = h.t;
-            if (alpha) alpha[i] = h.alpha;
-            if (beta) beta[i] = h.beta;
-        }
-        __syncwarp();
-    }
+    ClosestQueryPolicy pol = {o, d, tmin, tmax, prim, t, alpha, beta, S.slot_prim};
+    traverse_persistent<false, COUNT>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
 }
 
@@ -97,13 +122,8 @@ __global__ void __launch_bounds__(128) k_trace_any(DevScene S, int64_t n, const 
                                                    const double* __restrict__ tmin, const double* __restrict__ tmax, uint8_t* __restrict__ hit,
                                                    int32_t* fetch, unsigned long long* counters) {
     VisitCounters cnt = {0, 0};
-    for (;;) {
-        const int64_t i = (int64_t)warp_fetch(fetch) + lane_id();
-        if (i - lane_id() >= n) break;
-        if (i < n)
-            hit[i] = any_hit<COUNT>(S, mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), tmin[i], tmax[i], cnt) ? 1 : 0;
-        __syncwarp();
-    }
+    AnyQueryPolicy pol = {o, d, tmin, tmax, hit};
+    traverse_persistent<true, COUNT>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
 }
 
@@ -124,9 +144,9 @@ __global__ void k_sample_lights(DevScene S, int64_t n, const double* __restrict_
 /* ------------------------------------------------------------------------------------------------
  * wavefront integrator
  * ---------------------------------------------------------------------------------------------- */
-__device__ __forceinline__ d3 load3(const double* base, int64_t cap, int64_t i) { return mk3(base[i], base[cap + i], base[2 * cap + i]); }
-__device__ __forceinline__ void store3(double* base, int64_t cap, int64_t i, d3 v) {
-    base[i] = v.x; base[cap + i] = v.y; base[2 * cap + i] = v.z;
+__device__ __forceinline__ d3 ld3(const double* p) { return mk3(p[0], p[1], p[2]); }
+__device__ __forceinline__ void st3(double* p, d3 v) {
+    p[0] = v.x; p[1] = v.y; p[2] = v.z;
 }
 
 __global__ void __launch_bounds__(256) k_raygen(RenderConst rc, PathBuffers pb) {
@@ -136,71 +156,82 @@ __global__ void __launch_bounds__(256) k_raygen(RenderConst rc, PathBuffers pb) 
         /* Camera::GetRay: pixel centre, direction not normalised */
         const d3 ps = rc.pixel00 + ((double)i) * rc.dU + ((double)j) * rc.dV;
         const d3 dir = ps - rc.center;
-        store3(pb.ray, pb.cap, slot, rc.center);
-        store3(pb.ray + 3 * pb.cap, pb.cap, slot, dir);
-        store3(pb.T, pb.cap, slot, mk3(1.0, 1.0, 1.0));
-        store3(pb.L, pb.cap, slot, mk3(0.0, 0.0, 0.0));
-        pb.dim[slot] = 0u;
-        pb.flags[slot] = 0u;
+        st3(pb.rec[slot].o, rc.center);
+        st3(pb.rec[slot].d, dir);
+        st3(pb.rec[slot].T, mk3(1.0, 1.0, 1.0));
+        st3(pb.rec[slot].L, mk3(0.0, 0.0, 0.0));
+        pb.rec[slot].dim = 0u;
+        pb.rec[slot].flags = 0u;
     }
 }
 
-/* closest hit for every path in the bounce's queue (persistent warps, 32 rays per fetch), then the
- * terminal cases that need no BSDF, then one queue per material class for the shade kernels */
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce) {
-    BounceCtrl* ctrl = pb.ctrl + bounce;
-    const int32_t n = bounce == 0 ? rc.n_paths : ctrl->n_extend;
-    const int32_t* __restrict__ queue = pb.q_extend[bounce & 1];
-    VisitCounters cnt = {0, 0};
-    for (;;) {
-        const int32_t base = warp_fetch(&ctrl->fetch_extend);
-        if (base >= n) break;
-        const int32_t qi = base + lane_id();
-        const bool valid = qi < n;
+/* closest hit for every path in the bounce's queue (persistent warps with lane refill,
+ * traverse_warp.cuh), then the terminal cases that need no BSDF, then one queue per material class
+ * for the shade kernels */
+struct ExtendPolicy {
+    const DevScene& S;
+    const uint8_t* __restrict__ prim_class;
+    const RenderConst& rc;
+    const PathBuffers& pb;
+    BounceCtrl* ctrl;
+    const int32_t* __restrict__ queue;
+    int bounce;
+    int32_t slot;
+    __device__ __forceinline__ bool load(int32_t qi, d3& o, d3& d, double& t0, double& t1) {
+        slot = bounce == 0 ? qi : queue[qi];
+        o = ld3(pb.rec[slot].o);
+        d = ld3(pb.rec[slot].d);
+        t0 = 0.0001; /* Camera.cpp:125 */
+        t1 = (double)INFINITY;
+        return true;
+    }
+    __device__ __forceinline__ void retire(bool finished, int32_t, const Hit& h) {
         int cls = -1;
-        int32_t slot = 0;
-        if (valid) {
-            slot = bounce == 0 ? qi : queue[qi];
-            const d3 o = load3(pb.ray, pb.cap, slot), d = load3(pb.ray + 3 * pb.cap, pb.cap, slot);
-            Hit h;
-            closest_hit<COUNT>(S, o, d, 0.0001, (double)INFINITY, h, cnt); /* Camera.cpp:125 */
+        if (finished) {
             if (h.slot < 0) {
                 /* a primary miss returns the background (Camera.cpp:127); with NEE on, a scattered
                  * ray that misses adds nothing (Camera.cpp:187-196) */
                 const d3 bg = mk3(rc.background[0], rc.background[1], rc.background[2]);
-                if (bounce == 0) store3(pb.L, pb.cap, slot, bg);
-                else if (!rc.sample_lights) store3(pb.L, pb.cap, slot, load3(pb.L, pb.cap, slot) + load3(pb.T, pb.cap, slot) * bg);
+                if (bounce == 0) st3(pb.rec[slot].L, bg);
+                else if (!rc.sample_lights) st3(pb.rec[slot].L, ld3(pb.rec[slot].L) + ld3(pb.rec[slot].T) * bg);
             } else {
                 const int32_t prim = S.slot_prim[h.slot];
                 const int c = prim_class[prim];
                 if (c == CLS_EMISSIVE) {
                     /* an emitter ends the path (Camera.cpp:129-132); with NEE on, a scattered ray may
                      * collect it only if the scattering material skipped light sampling (:191-195) */
-                    const bool take = bounce == 0 || !rc.sample_lights || (pb.flags[slot] & PRT_FLAG_PREV_SKIP);
+                    const bool take = bounce == 0 || !rc.sample_lights || (pb.rec[slot].flags & PRT_FLAG_PREV_SKIP);
                     if (take) {
                         const DevMaterial* m = S.materials + S.shade[prim].material;
                         const d3 le = mk3(m->emission[0], m->emission[1], m->emission[2]);
-                        if (bounce == 0) store3(pb.L, pb.cap, slot, le);
-                        else store3(pb.L, pb.cap, slot, load3(pb.L, pb.cap, slot) + load3(pb.T, pb.cap, slot) * le);
+                        if (bounce == 0) st3(pb.rec[slot].L, le);
+                        else st3(pb.rec[slot].L, ld3(pb.rec[slot].L) + ld3(pb.rec[slot].T) * le);
                     }
                 } else if (c < CLS_SHADED) {
-                    pb.hit_prim[slot] = prim;
-                    pb.hit[slot] = h.t;
-                    pb.hit[pb.cap + slot] = h.alpha;
-                    pb.hit[2 * pb.cap + slot] = h.beta;
+                    pb.rec[slot].hit_prim = prim;
+                    pb.rec[slot].hit[0] = h.t;
+                    pb.rec[slot].hit[1] = h.alpha;
+                    pb.rec[slot].hit[2] = h.beta;
                     cls = c;
                 }
                 /* CLS_EMPTY: no NEE, Scatter returns false (Material.h:537-540): the path ends */
             }
         }
-        __syncwarp();
 #pragma unroll
         for (int c = 0; c < CLS_SHADED; ++c) {
             const int at = warp_push(&ctrl->n_mat[c], cls == c);
             if (at >= 0) pb.q_mat[c][at] = slot;
         }
     }
+};
+
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce) {
+    BounceCtrl* ctrl = pb.ctrl + bounce;
+    const int32_t n = bounce == 0 ? rc.n_paths : ctrl->n_extend;
+    VisitCounters cnt = {0, 0};
+    ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, pb.q_extend[bounce & 1], bounce, 0};
+    traverse_persistent<false, COUNT>(S, pol, &ctrl->fetch_extend, n, cnt);
     flush_counters<COUNT>(cnt, pb.counters);
 }
 
@@ -218,9 +249,9 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
         int32_t slot = 0;
         if (qi < n) {
             slot = queue[qi];
-            const int32_t prim = pb.hit_prim[slot];
-            const double t = pb.hit[slot], alpha = pb.hit[pb.cap + slot], beta = pb.hit[2 * pb.cap + slot];
-            const d3 ro = load3(pb.ray, pb.cap, slot), rd = load3(pb.ray + 3 * pb.cap, pb.cap, slot);
+            const int32_t prim = pb.rec[slot].hit_prim;
+            const double t = pb.rec[slot].hit[0], alpha = pb.rec[slot].hit[1], beta = pb.rec[slot].hit[2];
+            const d3 ro = ld3(pb.rec[slot].o), rd = ld3(pb.rec[slot].d);
             const TriShade* __restrict__ sh = S.shade + prim;
             const DevMaterial m = S.materials[sh->material];
             /* the HitRecord of Triangle::Hit (Triangle.cpp:76-80,111) */
@@ -235,8 +266,8 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
 
             Rng rng;
             rng.seed = stream_seed(rc.rng_key, (uint32_t)(slot % rc.npix), (uint32_t)(rc.sample_first + slot / rc.npix));
-            rng.dim = pb.dim[slot];
-            const d3 T = load3(pb.T, pb.cap, slot);
+            rng.dim = pb.rec[slot].dim;
+            const d3 T = ld3(pb.rec[slot].T);
 
             /* ---- next-event estimation (Camera.cpp:137-174) ---- */
             if (rc.sample_lights && !m.skip_light_sampling) {
@@ -255,9 +286,9 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
                     const double cos_theta = local_wi.z;
                     const double cos_theta_bar = dot(local_ln, -local_wi);
                     const d3 direct = emission * fr * cos_theta * cos_theta_bar / (distance * distance) / ls.pdf;
-                    store3(pb.shadow, pb.cap, slot, light_dir);
-                    pb.shadow[3 * pb.cap + slot] = distance;
-                    store3(pb.shadow + 4 * pb.cap, pb.cap, slot, T * direct);
+                    st3(pb.rec[slot].sdir, light_dir);
+                    pb.rec[slot].sdist = distance;
+                    st3(pb.rec[slot].scontrib, T * direct);
                     want_shadow = true;
                 }
             }
@@ -269,15 +300,15 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
                 else scatter_mirror(s, wo, att, out_dir);
                 /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
                 if (bounce < rc.max_depth) {
-                    store3(pb.ray, pb.cap, slot, s.position);
-                    store3(pb.ray + 3 * pb.cap, pb.cap, slot, out_dir);
-                    store3(pb.T, pb.cap, slot, T * att / rc.rr);
-                    pb.dim[slot] = rng.dim;
-                    pb.flags[slot] = m.skip_light_sampling ? PRT_FLAG_PREV_SKIP : 0u;
+                    st3(pb.rec[slot].o, s.position);
+                    st3(pb.rec[slot].d, out_dir);
+                    st3(pb.rec[slot].T, T * att / rc.rr);
+                    pb.rec[slot].dim = rng.dim;
+                    pb.rec[slot].flags = m.skip_light_sampling ? PRT_FLAG_PREV_SKIP : 0u;
                     want_extend = true;
                 }
             }
-            if (want_shadow && !want_extend) store3(pb.ray, pb.cap, slot, s.position); /* shadow ray origin */
+            if (want_shadow && !want_extend) st3(pb.rec[slot].o, s.position); /* shadow ray origin */
         }
         __syncwarp();
         const int a = warp_push(&ctrl->n_shadow, want_shadow);
@@ -291,37 +322,52 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
  * along the unit light direction and accepts iff something was hit and
  * distance - |ps - hit| < 1e-3, i.e. iff no surface lies closer than distance - 1e-3: an any-hit
  * query over [1e-3, distance - 1e-3]. PRT_RENDER_EXACT_VISIBILITY runs the literal test instead. */
+template <bool EXACT>
+struct ShadowPolicy {
+    const PathBuffers& pb;
+    const int32_t* __restrict__ queue;
+    int32_t slot;
+    d3 ps, dir;
+    double distance;
+    __device__ __forceinline__ bool load(int32_t qi, d3& o, d3& d, double& t0, double& t1) {
+        slot = queue[qi];
+        /* by now pb.ray holds the hit position as the origin of the next segment */
+        ps = ld3(pb.rec[slot].o);
+        dir = ld3(pb.rec[slot].sdir);
+        distance = pb.rec[slot].sdist;
+        o = ps;
+        d = dir;
+        t0 = 0.001;
+        t1 = EXACT ? DBL_MAX : distance - 0.001;
+        return true;
+    }
+    __device__ __forceinline__ void retire(bool finished, int32_t, const Hit& h) {
+        if (!finished) return;
+        bool visible;
+        if (EXACT) {
+            visible = false; /* a shadow ray that hits nothing reads an unset position: "not visible" */
+            if (h.slot >= 0) {
+                const d3 hp = ps + dir * h.t;
+                visible = distance - length(ps - hp) < 0.001;
+            }
+        } else {
+            visible = h.slot < 0;
+        }
+        if (visible) st3(pb.rec[slot].L, ld3(pb.rec[slot].L) + ld3(pb.rec[slot].scontrib));
+    }
+};
+
 template <bool COUNT>
 __global__ void __launch_bounds__(128) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = ctrl->n_shadow;
     VisitCounters cnt = {0, 0};
-    const bool exact = (rc.flags & PRT_RENDER_EXACT_VISIBILITY) != 0;
-    for (;;) {
-        const int32_t base = warp_fetch(&ctrl->fetch_shadow);
-        if (base >= n) break;
-        const int32_t qi = base + lane_id();
-        if (qi < n) {
-            const int32_t slot = pb.q_shadow[qi];
-            /* by now pb.ray holds the hit position as the origin of the next segment */
-            const d3 ps = load3(pb.ray, pb.cap, slot);
-            const d3 dir = load3(pb.shadow, pb.cap, slot);
-            const double distance = pb.shadow[3 * pb.cap + slot];
-            bool visible;
-            if (exact) {
-                Hit h;
-                closest_hit<COUNT>(S, ps, dir, 0.001, DBL_MAX, h, cnt);
-                visible = false; /* a shadow ray that hits nothing reads an unset position: "not visible" */
-                if (h.slot >= 0) {
-                    const d3 hp = ps + dir * h.t;
-                    visible = distance - length(ps - hp) < 0.001;
-                }
-            } else {
-                visible = !any_hit<COUNT>(S, ps, dir, 0.001, distance - 0.001, cnt);
-            }
-            if (visible) store3(pb.L, pb.cap, slot, load3(pb.L, pb.cap, slot) + load3(pb.shadow + 4 * pb.cap, pb.cap, slot));
-        }
-        __syncwarp();
+    if (rc.flags & PRT_RENDER_EXACT_VISIBILITY) {
+        ShadowPolicy<true> pol = {pb, pb.q_shadow, 0, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
+        traverse_persistent<false, COUNT>(S, pol, &ctrl->fetch_shadow, n, cnt);
+    } else {
+        ShadowPolicy<false> pol = {pb, pb.q_shadow, 0, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
+        traverse_persistent<true, COUNT>(S, pol, &ctrl->fetch_shadow, n, cnt);
     }
     flush_counters<COUNT>(cnt, pb.counters);
 }
@@ -330,7 +376,7 @@ __global__ void __launch_bounds__(128) k_shadow(DevScene S, RenderConst rc, Path
 __global__ void __launch_bounds__(256) k_accumulate(RenderConst rc, PathBuffers pb, double* __restrict__ rgb) {
     for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < rc.npix; pix += gridDim.x * blockDim.x) {
         d3 acc = mk3(rgb[3 * (int64_t)pix], rgb[3 * (int64_t)pix + 1], rgb[3 * (int64_t)pix + 2]);
-        for (int s = 0; s < rc.n_samples; ++s) acc = acc + load3(pb.L, pb.cap, (int64_t)s * rc.npix + pix) * rc.scale;
+        for (int s = 0; s < rc.n_samples; ++s) acc = acc + ld3(pb.rec[(int64_t)s * rc.npix + pix].L) * rc.scale;
         rgb[3 * (int64_t)pix] = acc.x; rgb[3 * (int64_t)pix + 1] = acc.y; rgb[3 * (int64_t)pix + 2] = acc.z;
     }
 }

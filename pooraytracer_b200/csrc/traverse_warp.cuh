@@ -1,0 +1,212 @@
+/*
+ * traverse_warp.cuh — the persistent-warp BVH walk used by the extend, shadow and ray-query kernels.
+ *
+ * What the ncu capture of the first version showed (profiles/r1_v0_k_extend_ncu_summary.txt): the
+ * scene lives in L1/L2 (DRAM throughput 3-8 %), the kernel is issue-bound with 6-7 of 32 lanes
+ * active per instruction on incoherent bounces, and 40 % of the issue slots go to the FP64 pipe,
+ * most of them for box tests. Hence:
+ *
+ *   1. lanes are refilled: a lane whose ray is finished takes the next ray of the queue while its
+ *      neighbours keep walking (one warp-aggregated atomic per refill), instead of idling until the
+ *      slowest of 32 rays is done;
+ *   2. while-while: every lane first descends inner nodes until it holds a leaf, then all lanes
+ *      intersect their leaves together, so the node code and the triangle code are not serialised
+ *      against each other inside one loop body;
+ *   3. the box test runs in FP32 with explicit outward padding and only ever over-approximates the
+ *      reference's FP64 slab test (AABB.cpp:38-64), which keeps the FP64 pipe for the one thing that
+ *      must carry the reference's bits: Triangle::Hit (tri_test, traverse.cuh).
+ *
+ * Box test error budget. Node bounds are FP32, rounded outward from the FP64 boxes on the host. With
+ * o32 = fl32(o), inv32 = fl32(1/d) (|inv32| clamped to 1e30 so 0 * inf never appears):
+ *     fl32(fl32(b - o32) * inv32) = (b - o) / d * (1 + e)^3  -  (o32 - o) / d * (1 + e)^3,   |e| <= 2^-24
+ * so |computed - exact| <= |computed| * 2^-21 + |o32| * |inv32| * 2^-23 (both with > 2x margin). Entry
+ * distances are lowered and exit distances raised by that amount, tmin is rounded down and the
+ * current closest t rounded up to FP32: a box is skipped only if the padded interval is empty, which
+ * implies that the exact interval of the enclosed FP64 box is empty too.
+ */
+#ifndef PRT_TRAVERSE_WARP_CUH
+#define PRT_TRAVERSE_WARP_CUH
+
+#include "traverse.cuh"
+
+namespace prt {
+
+#define PRT_DONE 0x7fffffff      /* `cur` of a lane whose walk is over */
+#define PRT_BOX_EPS 4.76837158e-7f /* 2^-21 */
+#ifndef PRT_REFILL_BELOW
+#define PRT_REFILL_BELOW 24      /* refill idle lanes once fewer than this many lanes hold a ray */
+#endif
+
+struct RayF32 { /* the FP32 side of a ray, for box tests only */
+    float ox, oy, oz, ix, iy, iz, ex, ey, ez;
+};
+
+__device__ __forceinline__ float clamp_inv(double d) {
+    float i = (float)(1.0 / d);
+    if (!(fabsf(i) <= 1e30f)) i = signbit(d) ? -1e30f : 1e30f; /* inf (d == +-0, denormal) and NaN */
+    return i;
+}
+__device__ __forceinline__ RayF32 make_ray_f32(d3 o, d3 d) {
+    RayF32 r;
+    r.ox = (float)o.x; r.oy = (float)o.y; r.oz = (float)o.z;
+    r.ix = clamp_inv(d.x); r.iy = clamp_inv(d.y); r.iz = clamp_inv(d.z);
+    r.ex = __fmul_ru(__fmul_ru(fabsf(r.ox), fabsf(r.ix)), 1.1920929e-7f); /* |o32| |inv32| 2^-23 */
+    r.ey = __fmul_ru(__fmul_ru(fabsf(r.oy), fabsf(r.iy)), 1.1920929e-7f);
+    r.ez = __fmul_ru(__fmul_ru(fabsf(r.oz), fabsf(r.iz)), 1.1920929e-7f);
+    return r;
+}
+
+/* padded slab interval of one axis: [near - pad, far + pad] */
+__device__ __forceinline__ void slab_f32(float blo, float bhi, float o, float inv, float err, float& tn, float& tf) {
+    const float t0 = (blo - o) * inv, t1 = (bhi - o) * inv;
+    const float n = fminf(t0, t1), f = fmaxf(t0, t1);
+    tn = fmaf(-PRT_BOX_EPS, fabsf(n), n) - err;
+    tf = fmaf(PRT_BOX_EPS, fabsf(f), f) + err;
+}
+__device__ __forceinline__ bool box_f32(float lx, float ly, float lz, float hx, float hy, float hz, const RayF32& r, float tmin32,
+                                        float tbest32, float& entry) {
+    float nx, fx, ny, fy, nz, fz;
+    slab_f32(lx, hx, r.ox, r.ix, r.ex, nx, fx);
+    slab_f32(ly, hy, r.oy, r.iy, r.ey, ny, fy);
+    slab_f32(lz, hz, r.oz, r.iz, r.ez, nz, fz);
+    /* fmaxf / fminf drop NaNs (inf - inf of an overflowed bound): such an axis does not constrain */
+    entry = fmaxf(fmaxf(nx, ny), fmaxf(nz, tmin32));
+    const float exit = fminf(fminf(fx, fy), fminf(fz, tbest32));
+    return entry <= exit;
+}
+
+/*
+ * The persistent loop. Policy P supplies the rays and consumes the results:
+ *     bool P::load(int32_t qi, d3& o, d3& d, double& tmin, double& tmax)   per lane; false = skip
+ *     void P::retire(bool finished, int32_t qi, const Hit& hit)            ALL lanes call it together;
+ *                                                                          lanes with finished == true
+ *                                                                          carry a completed ray
+ * `cursor` is the queue's fetch counter (zeroed by the host), `n` the queue length.
+ * Results are the reference's (see traverse.cuh): boundary and equal-t hits go through
+ * trace_reference before they are retired.
+ */
+template <bool ANY, bool COUNT, class P>
+__device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, int32_t* cursor, int32_t n, VisitCounters& cnt) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int32_t stack[PRT_STACK];
+    int sp = 0;
+    int32_t cur = PRT_DONE;
+    int32_t qi = -1;
+    bool has_ray = false, exhausted = false, recheck = false;
+    d3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
+    double tmin = 0.0, tmax = 0.0, tbest = 0.0;
+    float tmin32 = 0.f, tbest32 = 0.f;
+    RayF32 rf = make_ray_f32(o, d);
+    Hit hit;
+    hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
+    const bool use_sah = S.nodes2 != nullptr;
+
+    for (;;) {
+        /* ---- retire finished lanes, refill idle ones ---- */
+        const bool finished = has_ray && cur == PRT_DONE;
+        if (finished) {
+            if (use_sah && recheck) {
+                if (ANY) trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+                else trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+            }
+            has_ray = false;
+        }
+        __syncwarp();
+        pol.retire(finished, qi, hit);
+        if (!exhausted) {
+            const unsigned need = __ballot_sync(FULL, !has_ray);
+            int32_t base = 0;
+            const int leader = __ffs(need) - 1;
+            if (lane == leader) base = atomicAdd(cursor, __popc(need));
+            base = __shfl_sync(FULL, base, leader);
+            if (base + __popc(need) >= n) exhausted = true; /* nothing left after this batch */
+            if (!has_ray) {
+                const int32_t mine = base + __popc(need & ((1u << lane) - 1u));
+                if (mine < n) {
+                    qi = mine;
+                    if (pol.load(qi, o, d, tmin, tmax)) {
+                        has_ray = true;
+                        recheck = false;
+                        hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
+                        tbest = tmax;
+                        sp = 0;
+                        if (use_sah) {
+                            rf = make_ray_f32(o, d);
+                            tmin32 = __double2float_rd(tmin);
+                            tbest32 = __double2float_ru(tbest);
+                            cur = S.n_tris > 0 ? 0 : PRT_DONE;
+                        } else {
+                            /* PRT_ACCEL_REFERENCE_BVH2: the reference's own walk, one ray per lane */
+                            if (ANY) trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+                            else trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+                            cur = PRT_DONE;
+                        }
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(FULL, has_ray) == 0) {
+            if (exhausted) break;
+            continue;
+        }
+
+        /* ---- walk until enough lanes have run dry ---- */
+        for (;;) {
+            /* inner nodes: descend until this lane holds a leaf or is done */
+            while (cur >= 0 && cur != PRT_DONE) {
+                const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes2 + cur);
+                const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+                const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
+                if (COUNT) cnt.nodes++;
+                float e0, e1;
+                const bool h0 = box_f32(a.x, a.y, a.z, a.w, b.x, b.y, rf, tmin32, tbest32, e0);
+                const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
+                if (h0 && h1) {
+                    const bool swap = e1 < e0;
+                    if (sp < PRT_STACK) stack[sp++] = swap ? ch.x : ch.y;
+                    cur = swap ? ch.y : ch.x;
+                } else if (h0) {
+                    cur = ch.x;
+                } else if (h1) {
+                    cur = ch.y;
+                } else {
+                    cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                }
+            }
+            /* leaves */
+            if (cur < 0) {
+                const int32_t code = ~cur;
+                const int32_t first = code >> 3, count = (code & 7) + 1;
+                bool done = false;
+                for (int32_t i = 0; i < count; ++i) {
+                    double t, al, be;
+                    if (COUNT) cnt.tris++;
+                    if (tri_test(S.tris + first + i, o, d, tmin, tbest, t, al, be)) {
+                        if (ANY) {
+                            /* a boundary hit may be one the reference's boxes reject: keep looking
+                             * for an interior one, let the reference decide if none turns up */
+                            if (on_boundary(al, be)) { recheck = true; continue; }
+                            hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
+                            recheck = false;
+                            done = true;
+                            break;
+                        }
+                        recheck = hit.slot >= 0 && t == tbest; /* same t, another triangle */
+                        hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
+                        tbest = t;
+                        tbest32 = __double2float_ru(t);
+                    }
+                }
+                cur = (done || sp == 0) ? PRT_DONE : stack[--sp];
+            }
+            if (cur == PRT_DONE && has_ray && !ANY && hit.slot >= 0 && on_boundary(hit.alpha, hit.beta)) recheck = true;
+            const unsigned walking = __ballot_sync(FULL, has_ray && cur != PRT_DONE);
+            if (walking == 0) break;
+            if (!exhausted && __popc(walking) < PRT_REFILL_BELOW) break;
+        }
+    }
+}
+
+}  // namespace prt
+#endif
