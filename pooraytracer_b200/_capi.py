@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libprt_b200.so")
+LIB_PATH = os.environ.get("PRT_B200_LIB") or os.path.join(HERE, "libprt_b200.so")  # override: A/B builds of the same ABI
 
 PRT_OK = 0
 PRT_ERR_INVALID_ARGUMENT = -1

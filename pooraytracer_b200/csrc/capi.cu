@@ -140,7 +140,7 @@ LaunchConfig launch_config(const prt_context* ctx) {
     LaunchConfig lc;
     lc.sm_count = ctx->sm_count;
     const char* env = std::getenv("PRT_BLOCKS_PER_SM");
-    lc.trace_blocks_per_sm = env ? std::max(1, std::atoi(env)) : 8;
+    lc.trace_blocks_per_sm = env ? std::max(1, std::atoi(env)) : 0; /* 0 = whatever is resident */
     lc.stage_events = nullptr;
     return lc;
 }

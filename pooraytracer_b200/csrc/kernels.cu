@@ -23,12 +23,18 @@
 #include <cuda_runtime.h>
 #include <float.h>
 
+#include <unordered_map>
+
 #include "../../include/prt_b200.h"
 #include "launch.h"
 #include "rng.cuh"
 #include "shading.cuh"
 #include "traverse.cuh"
 #include "traverse_warp.cuh"
+
+#ifndef PRT_TRAVERSE_MIN_BLOCKS
+#define PRT_TRAVERSE_MIN_BLOCKS 6
+#endif
 
 namespace prt {
 
@@ -107,7 +113,7 @@ struct AnyQueryPolicy {
 };
 
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_trace_closest(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                        const double* __restrict__ tmin, const double* __restrict__ tmax,
                                                        int32_t* __restrict__ prim, double* __restrict__ t, double* __restrict__ alpha,
                                                        double* __restrict__ beta, int32_t* fetch, unsigned long long* counters) {
@@ -118,7 +124,7 @@ __global__ void __launch_bounds__(128) k_trace_closest(DevScene S, int64_t n, co
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                    const double* __restrict__ tmin, const double* __restrict__ tmax, uint8_t* __restrict__ hit,
                                                    int32_t* fetch, unsigned long long* counters) {
     VisitCounters cnt = {0, 0};
@@ -226,7 +232,7 @@ struct ExtendPolicy {
 };
 
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce) {
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = bounce == 0 ? rc.n_paths : ctrl->n_extend;
     VisitCounters cnt = {0, 0};
@@ -358,7 +364,7 @@ struct ShadowPolicy {
 };
 
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = ctrl->n_shadow;
     VisitCounters cnt = {0, 0};
@@ -421,22 +427,44 @@ __global__ void __launch_bounds__(256) k_resolve(const double* __restrict__ rgb,
 /* ------------------------------------------------------------------------------------------------
  * launchers
  * ---------------------------------------------------------------------------------------------- */
+#ifndef PRT_TRAVERSE_MIN_BLOCKS
+#define PRT_TRAVERSE_MIN_BLOCKS 6
+#endif
+
+/* persistent kernels get exactly as many blocks as can be resident (148 SMs x occupancy), never a
+ * second wave; small queues get fewer */
+template <typename K>
+static int persistent_grid(K kernel, int block, const LaunchConfig& lc, int64_t items) {
+    static std::unordered_map<const void*, int> cache;
+    const void* key = (const void*)kernel;
+    auto it = cache.find(key);
+    int per_sm;
+    if (it == cache.end()) {
+        per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        cache[key] = per_sm;
+    } else {
+        per_sm = it->second;
+    }
+    if (lc.trace_blocks_per_sm > 0 && per_sm > lc.trace_blocks_per_sm) per_sm = lc.trace_blocks_per_sm;
+    const int64_t cap = (int64_t)per_sm * lc.sm_count;
+    int64_t want = (items + block - 1) / block;
+    if (want < 1) want = 1;
+    return (int)(want < cap ? want : cap);
+}
+
 void launch_trace_closest(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
                           int32_t* prim, double* t, double* alpha, double* beta, int32_t* fetch, unsigned long long* counters,
                           const LaunchConfig& lc, cudaStream_t st) {
     if (n <= 0) return;
-    int64_t want = (n + 127) / 128;
-    const int grid = (int)(want < (int64_t)lc.sm_count * lc.trace_blocks_per_sm ? want : (int64_t)lc.sm_count * lc.trace_blocks_per_sm);
-    if (counters) k_trace_closest<true><<<grid, 128, 0, st>>>(S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters);
-    else k_trace_closest<false><<<grid, 128, 0, st>>>(S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters);
+    if (counters) k_trace_closest<true><<<persistent_grid(k_trace_closest<true>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters);
+    else k_trace_closest<false><<<persistent_grid(k_trace_closest<false>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters);
 }
 void launch_trace_any(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
                       uint8_t* hit, int32_t* fetch, unsigned long long* counters, const LaunchConfig& lc, cudaStream_t st) {
     if (n <= 0) return;
-    int64_t want = (n + 127) / 128;
-    const int grid = (int)(want < (int64_t)lc.sm_count * lc.trace_blocks_per_sm ? want : (int64_t)lc.sm_count * lc.trace_blocks_per_sm);
-    if (counters) k_trace_any<true><<<grid, 128, 0, st>>>(S, n, o, d, tmin, tmax, hit, fetch, counters);
-    else k_trace_any<false><<<grid, 128, 0, st>>>(S, n, o, d, tmin, tmax, hit, fetch, counters);
+    if (counters) k_trace_any<true><<<persistent_grid(k_trace_any<true>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, hit, fetch, counters);
+    else k_trace_any<false><<<persistent_grid(k_trace_any<false>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, hit, fetch, counters);
 }
 void launch_sample_lights(const DevScene& S, int64_t n, const double* origins, const double* u, double* position, double* normal,
                           uint8_t* front, double* pdf, int32_t* prim, cudaStream_t st) {
@@ -450,25 +478,30 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int n_bounces = rc.max_depth + 1;
     cudaMemsetAsync(pb.ctrl, 0, sizeof(BounceCtrl) * (size_t)(n_bounces + 1), st);
     const bool count = (rc.flags & PRT_RENDER_COUNTERS) != 0;
-    const int persistent = lc.sm_count * lc.trace_blocks_per_sm;
-    int64_t want = ((int64_t)rc.n_paths + 127) / 128;
-    const int grid_paths = (int)(want < persistent ? want : persistent);
-    k_raygen<<<(int)(((int64_t)rc.n_paths + 255) / 256 < lc.sm_count * 8 ? ((int64_t)rc.n_paths + 255) / 256 : lc.sm_count * 8), 256, 0, st>>>(rc, pb);
+    const int g_extend = count ? persistent_grid(k_extend<true>, 128, lc, rc.n_paths) : persistent_grid(k_extend<false>, 128, lc, rc.n_paths);
+    const int g_shadow = count ? persistent_grid(k_shadow<true>, 128, lc, rc.n_paths) : persistent_grid(k_shadow<false>, 128, lc, rc.n_paths);
+    LaunchConfig shade_lc = lc;
+    shade_lc.trace_blocks_per_sm = 0;
+    const int g_shade0 = persistent_grid(k_shade<CLS_LAMBERT>, 128, shade_lc, rc.n_paths);
+    const int g_shade1 = persistent_grid(k_shade<CLS_PHONG>, 128, shade_lc, rc.n_paths);
+    const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR>, 128, shade_lc, rc.n_paths);
+    const int64_t rg = ((int64_t)rc.n_paths + 255) / 256;
+    k_raygen<<<(int)(rg < lc.sm_count * 8 ? rg : lc.sm_count * 8), 256, 0, st>>>(rc, pb);
     ++launches;
     cudaEvent_t* ev = lc.stage_events;
     for (int b = 0; b < n_bounces; ++b) {
         if (ev) cudaEventRecord(ev[4 * b], st);
-        if (count) k_extend<true><<<grid_paths, 128, 0, st>>>(S, prim_class, rc, pb, b);
-        else k_extend<false><<<grid_paths, 128, 0, st>>>(S, prim_class, rc, pb, b);
+        if (count) k_extend<true><<<g_extend, 128, 0, st>>>(S, prim_class, rc, pb, b);
+        else k_extend<false><<<g_extend, 128, 0, st>>>(S, prim_class, rc, pb, b);
         if (ev) cudaEventRecord(ev[4 * b + 1], st);
-        k_shade<CLS_LAMBERT><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
-        k_shade<CLS_PHONG><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
-        k_shade<CLS_MIRROR><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
+        k_shade<CLS_LAMBERT><<<g_shade0, 128, 0, st>>>(S, rc, pb, b);
+        k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b);
+        k_shade<CLS_MIRROR><<<g_shade2, 128, 0, st>>>(S, rc, pb, b);
         launches += 4;
         if (ev) cudaEventRecord(ev[4 * b + 2], st);
         if (rc.sample_lights) {
-            if (count) k_shadow<true><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
-            else k_shadow<false><<<grid_paths, 128, 0, st>>>(S, rc, pb, b);
+            if (count) k_shadow<true><<<g_shadow, 128, 0, st>>>(S, rc, pb, b);
+            else k_shadow<false><<<g_shadow, 128, 0, st>>>(S, rc, pb, b);
             ++launches;
         }
         if (ev) cudaEventRecord(ev[4 * b + 3], st);

@@ -17,9 +17,10 @@
  *      must carry the reference's bits: Triangle::Hit (tri_test, traverse.cuh).
  *
  * Box test error budget. Node bounds are FP32, rounded outward from the FP64 boxes on the host. With
- * o32 = fl32(o), inv32 = fl32(1/d) (|inv32| clamped to 1e30 so 0 * inf never appears):
- *     fl32(fl32(b - o32) * inv32) = (b - o) / d * (1 + e)^3  -  (o32 - o) / d * (1 + e)^3,   |e| <= 2^-24
- * so |computed - exact| <= |computed| * 2^-21 + |o32| * |inv32| * 2^-23 (both with > 2x margin). Entry
+ * o32 = fl32(o), inv32 = fl32(1/d) (|inv32| clamped to 1e30 so 0 * inf never appears), p = fl32(o32 inv32):
+ *     fma(b, inv32, -p) = [ (b - o) / d  +  (o - o32) / d  +  (o32 inv32 - p) / 1 ] (1 + e)^2,   |e| <= 2^-24
+ * and |o - o32| <= |o| 2^-24, |o32 inv32 - p| <= |o32 inv32| 2^-24, so
+ *     |computed - exact| <= |computed| * 2^-21 + |o32| * |inv32| * 2^-22     (both with > 2x margin). Entry
  * distances are lowered and exit distances raised by that amount, tmin is rounded down and the
  * current closest t rounded up to FP32: a box is skipped only if the padded interval is empty, which
  * implies that the exact interval of the enclosed FP64 box is empty too.
@@ -37,8 +38,10 @@ namespace prt {
 #define PRT_REFILL_BELOW 24      /* refill idle lanes once fewer than this many lanes hold a ray */
 #endif
 
-struct RayF32 { /* the FP32 side of a ray, for box tests only */
-    float ox, oy, oz, ix, iy, iz, ex, ey, ez;
+struct RayF32 { /* the FP32 side of a ray, for box tests only: t = b * inv - o * inv */
+    float ix, iy, iz;    /* fl32(1 / d), clamped */
+    float ox, oy, oz;    /* fl32(o32 * inv32) */
+    float err;           /* max over the axes of |o32| |inv32| 2^-22 (rounded up) */
 };
 
 __device__ __forceinline__ float clamp_inv(double d) {
@@ -48,30 +51,28 @@ __device__ __forceinline__ float clamp_inv(double d) {
 }
 __device__ __forceinline__ RayF32 make_ray_f32(d3 o, d3 d) {
     RayF32 r;
-    r.ox = (float)o.x; r.oy = (float)o.y; r.oz = (float)o.z;
+    const float ox = (float)o.x, oy = (float)o.y, oz = (float)o.z;
     r.ix = clamp_inv(d.x); r.iy = clamp_inv(d.y); r.iz = clamp_inv(d.z);
-    r.ex = __fmul_ru(__fmul_ru(fabsf(r.ox), fabsf(r.ix)), 1.1920929e-7f); /* |o32| |inv32| 2^-23 */
-    r.ey = __fmul_ru(__fmul_ru(fabsf(r.oy), fabsf(r.iy)), 1.1920929e-7f);
-    r.ez = __fmul_ru(__fmul_ru(fabsf(r.oz), fabsf(r.iz)), 1.1920929e-7f);
+    r.ox = ox * r.ix; r.oy = oy * r.iy; r.oz = oz * r.iz;
+    const float ex = __fmul_ru(fabsf(ox), fabsf(r.ix)), ey = __fmul_ru(fabsf(oy), fabsf(r.iy)), ez = __fmul_ru(fabsf(oz), fabsf(r.iz));
+    r.err = __fmul_ru(fmaxf(ex, fmaxf(ey, ez)), 2.3841858e-7f); /* 2^-22 */
     return r;
 }
 
-/* padded slab interval of one axis: [near - pad, far + pad] */
-__device__ __forceinline__ void slab_f32(float blo, float bhi, float o, float inv, float err, float& tn, float& tf) {
-    const float t0 = (blo - o) * inv, t1 = (bhi - o) * inv;
-    const float n = fminf(t0, t1), f = fmaxf(t0, t1);
-    tn = fmaf(-PRT_BOX_EPS, fabsf(n), n) - err;
-    tf = fmaf(PRT_BOX_EPS, fabsf(f), f) + err;
-}
+/* Padded FP32 slab test. Per axis t = fma(b, inv32, -o32 * inv32); with E = the largest computed near
+ * value and X = the smallest computed far value, the exact entry distance is >= the exact near value
+ * of E's axis >= E - |E| eps - err, and the exact exit distance <= X + |X| eps + err, so padding the
+ * two extremes once is as safe as padding all six values. fmaxf / fminf drop NaNs (inf - inf of an
+ * overflowed bound): such an axis does not constrain. */
 __device__ __forceinline__ bool box_f32(float lx, float ly, float lz, float hx, float hy, float hz, const RayF32& r, float tmin32,
                                         float tbest32, float& entry) {
-    float nx, fx, ny, fy, nz, fz;
-    slab_f32(lx, hx, r.ox, r.ix, r.ex, nx, fx);
-    slab_f32(ly, hy, r.oy, r.iy, r.ey, ny, fy);
-    slab_f32(lz, hz, r.oz, r.iz, r.ez, nz, fz);
-    /* fmaxf / fminf drop NaNs (inf - inf of an overflowed bound): such an axis does not constrain */
-    entry = fmaxf(fmaxf(nx, ny), fmaxf(nz, tmin32));
-    const float exit = fminf(fminf(fx, fy), fminf(fz, tbest32));
+    const float ax = fmaf(lx, r.ix, -r.ox), bx = fmaf(hx, r.ix, -r.ox);
+    const float ay = fmaf(ly, r.iy, -r.oy), by = fmaf(hy, r.iy, -r.oy);
+    const float az = fmaf(lz, r.iz, -r.oz), bz = fmaf(hz, r.iz, -r.oz);
+    const float E = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+    const float X = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    entry = fmaxf(fmaf(-PRT_BOX_EPS, fabsf(E), E) - r.err, tmin32);
+    const float exit = fminf(fmaf(PRT_BOX_EPS, fabsf(X), X) + r.err, tbest32);
     return entry <= exit;
 }
 

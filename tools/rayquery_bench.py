@@ -1,0 +1,103 @@
+#!/usr/bin/env python
+"""Ray-query microbench (BASELINE.json configs[4]): 2^24 random / coherent rays against the procedural
+`terrain` and `soup` meshes (1 M and 10 M triangles), closest-hit and any-hit, device-resident inputs,
+CUDA-event timing inside the library (prt_stats.gpu_ms). One JSON line per case.
+
+  python tools/rayquery_bench.py --tris 1 --rays 24 [--mesh terrain|soup] [--check N]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tris", type=int, default=1, help="millions of triangles (1 or 10)")
+    ap.add_argument("--rays", type=int, default=24, help="log2 of the ray count")
+    ap.add_argument("--mesh", default="terrain")
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--check", type=int, default=0, help="compare the first N rays with the CPU oracle")
+    ap.add_argument("--max-leaf", type=int, default=0)
+    a = ap.parse_args()
+    import torch
+    from pooraytracer_b200 import Context, Scene, _capi as capi, scenes
+
+    n = 1 << a.rays
+    if a.mesh == "terrain":
+        sc = scenes.terrain(1000, 500) if a.tris == 1 else scenes.terrain(2500, 2000)
+    else:
+        sc = scenes.soup(a.tris * 1_000_000)
+    t0 = time.time()
+    ctx = Context(0)
+    scene = Scene(ctx, sc, accel=None)
+    t_create = time.time() - t0
+    t0 = time.time()
+    import ctypes as C
+    o_ = capi.PrtBuildOpts()
+    o_.accel = capi.ACCEL_SAH_BVH2
+    o_.reserved[0] = a.max_leaf
+    rc = scene.lib.prt_scene_commit(scene.handle, C.byref(o_))
+    assert rc == 0, scene.lib.prt_last_error()
+    t_commit = time.time() - t0
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    diag = float(np.linalg.norm(sc.vertices.reshape(-1, 3).max(0) - sc.vertices.reshape(-1, 3).min(0)))
+    for kind in ("random", "coherent"):
+        if kind == "random":
+            o, d = scenes.random_rays(sc, n)
+        else:
+            side = 1 << (a.rays // 2)
+            o, d = scenes.camera_rays(sc.camera, side, n // side)
+        do, dd = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+        tmin = torch.full((n,), 1e-4, dtype=torch.float64, device="cuda")
+        tmax = torch.full((n,), float("inf"), dtype=torch.float64, device="cuda")
+        prim = torch.empty(n, dtype=torch.int32, device="cuda")
+        t = torch.empty(n, dtype=torch.float64, device="cuda")
+        al, be = torch.empty_like(t), torch.empty_like(t)
+        hit = torch.empty(n, dtype=torch.uint8, device="cuda")
+        tmax_any = torch.from_numpy(scenes.hash_uniform(n, 5, 1) * diag).cuda()
+        tmin_any = torch.full((n,), 1e-3, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        for query in ("closest", "any"):
+            def run():
+                if query == "closest":
+                    rc = scene.lib.prt_trace_closest_device(scene.handle, n, do.data_ptr(), dd.data_ptr(), tmin.data_ptr(), tmax.data_ptr(),
+                                                            prim.data_ptr(), t.data_ptr(), al.data_ptr(), be.data_ptr(), None)
+                else:
+                    rc = scene.lib.prt_trace_any_device(scene.handle, n, do.data_ptr(), dd.data_ptr(), tmin_any.data_ptr(), tmax_any.data_ptr(),
+                                                        hit.data_ptr(), None)
+                assert rc == 0, scene.lib.prt_last_error()
+                return scene.stats()
+            scene.set_counters(True)
+            st = run()
+            nodes, tris = st.node_visits, st.tri_tests
+            scene.set_counters(False)
+            run()
+            ms = min(run().gpu_ms for _ in range(a.reps))
+            alg = nodes * st.node_bytes + tris * st.tri_bytes
+            line = {"case": f"{a.mesh}-{sc.n_triangles} {kind} {query}", "rays": n, "mrays_s": n / ms / 1e3, "ms": ms,
+                    "nodes_per_ray": nodes / n, "tris_per_ray": tris / n, "bytes_per_ray": alg / n,
+                    "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                 "frac": alg / (ms * 1e-3) / 1e9 / peak},
+                    "hit_fraction": float((prim >= 0).float().mean().item()) if query == "closest" else float(hit.float().mean().item()),
+                    "scene_create_s": t_create, "scene_commit_s": t_commit, "n_nodes": st.n_nodes}
+            if a.check and query == "closest" and kind == "random":
+                sys.path.insert(0, os.path.join(ROOT, "tests"))
+                import oracle_lib as ol
+                O = ol.OracleScene("orc", sc, 0)
+                m = a.check
+                want = O.trace_closest(o[:m], d[:m], 1e-4, np.inf, nthreads=os.cpu_count() or 4)
+                got = (prim[:m].cpu().numpy(), t[:m].cpu().numpy(), al[:m].cpu().numpy(), be[:m].cpu().numpy())
+                line["oracle_check"] = {"rays": m, "bit_exact": bool(all(np.array_equal(x, y) for x, y in zip(got, want)))}
+            print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
