@@ -172,6 +172,7 @@ def run_b200(a):
     import torch
     import torch.distributed as dist
     from pooraytracer_b200 import Context, Scene, _capi as capi, make_camera, make_params
+    from pooraytracer_b200.sharding import sample_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -195,9 +196,9 @@ def run_b200(a):
     acc = torch.zeros(npix * 3, dtype=torch.float64, device="cuda")
 
     def params(step, flags=0):
-        # global sample range of this step, sharded over ranks: rank r renders [b + r*S, b + (r+1)*S)
-        b = step * S * world + rank * S
-        return make_params(TOTAL_SPP, a.depth, rr=RR, rng_key=20251104, spp_begin=b, spp_end=b + S, flags=flags)
+        # global sample range of this step, sharded over ranks (pooraytracer_b200/sharding.py)
+        b, e = sample_range(step, S, rank, world)
+        return make_params(TOTAL_SPP, a.depth, rr=RR, rng_key=20251104, spp_begin=b, spp_end=e, flags=flags)
 
     def one_step(step, flags=0):
         scene.render_device(cam, params(step, flags), acc.data_ptr(), stream.cuda_stream)
