@@ -3,7 +3,7 @@
  *
  *   k_trace_closest / k_trace_any   ray-query batches = Hittable::Hit on `world` (Source/Hittable.h:34)
  *   k_sample_lights                 Hittable::Sample on `lights` (Source/Hittable.h:36)
- *   k_raygen                        Camera::GetRay (Source/Camera.cpp:108-117)
+ *   camera_ray                      Camera::GetRay (Source/Camera.cpp:108-117), fused into bounce 0 of k_extend
  *   k_extend                        closest hit of every live path + the terminal cases of
  *                                   Camera::RayColor (miss / emitter, Camera.cpp:125-132,187-196),
  *                                   hits binned by material class
@@ -38,6 +38,9 @@
 
 namespace prt {
 
+#ifndef PRT_EXTEND_DEFER
+#define PRT_EXTEND_DEFER 0
+#endif
 #define PRT_FLAG_PREV_SKIP 1u /* the vertex that scattered this ray skipped light sampling */
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
@@ -82,6 +85,11 @@ struct ClosestQueryPolicy {
     int32_t* prim;
     double *t, *alpha, *beta;
     const int32_t* slot_prim;
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return qi; }
+    __device__ __forceinline__ void prefetch(int32_t i) const {
+        prefetch_l2(o + 3 * (int64_t)i);
+        prefetch_l2(d + 3 * (int64_t)i);
+    }
     __device__ __forceinline__ bool load(int32_t i, d3& ro, d3& rd, double& t0, double& t1) const {
         ro = mk3(o[3 * (int64_t)i], o[3 * (int64_t)i + 1], o[3 * (int64_t)i + 2]);
         rd = mk3(d[3 * (int64_t)i], d[3 * (int64_t)i + 1], d[3 * (int64_t)i + 2]);
@@ -96,10 +104,16 @@ struct ClosestQueryPolicy {
         if (alpha) alpha[i] = h.alpha;
         if (beta) beta[i] = h.beta;
     }
+    __device__ __forceinline__ void finish() const {}
 };
 struct AnyQueryPolicy {
     const double *o, *d, *tmin, *tmax;
     uint8_t* hit;
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return qi; }
+    __device__ __forceinline__ void prefetch(int32_t i) const {
+        prefetch_l2(o + 3 * (int64_t)i);
+        prefetch_l2(d + 3 * (int64_t)i);
+    }
     __device__ __forceinline__ bool load(int32_t i, d3& ro, d3& rd, double& t0, double& t1) const {
         ro = mk3(o[3 * (int64_t)i], o[3 * (int64_t)i + 1], o[3 * (int64_t)i + 2]);
         rd = mk3(d[3 * (int64_t)i], d[3 * (int64_t)i + 1], d[3 * (int64_t)i + 2]);
@@ -110,6 +124,7 @@ struct AnyQueryPolicy {
     __device__ __forceinline__ void retire(bool finished, int32_t i, const Hit& h) const {
         if (finished) hit[i] = h.slot >= 0 ? 1 : 0;
     }
+    __device__ __forceinline__ void finish() const {}
 };
 
 template <bool COUNT>
@@ -155,25 +170,48 @@ __device__ __forceinline__ void st3(double* p, d3 v) {
     p[0] = v.x; p[1] = v.y; p[2] = v.z;
 }
 
-__global__ void __launch_bounds__(256) k_raygen(RenderConst rc, PathBuffers pb) {
-    for (int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; slot < rc.n_paths; slot += (int64_t)gridDim.x * blockDim.x) {
-        const int pix = (int)(slot % rc.npix);
-        const int i = pix % rc.width, j = pix / rc.width;
-        /* Camera::GetRay: pixel centre, direction not normalised */
-        const d3 ps = rc.pixel00 + ((double)i) * rc.dU + ((double)j) * rc.dV;
-        const d3 dir = ps - rc.center;
-        st3(pb.rec[slot].o, rc.center);
-        st3(pb.rec[slot].d, dir);
-        st3(pb.rec[slot].T, mk3(1.0, 1.0, 1.0));
-        st3(pb.rec[slot].L, mk3(0.0, 0.0, 0.0));
-        pb.rec[slot].dim = 0u;
-        pb.rec[slot].flags = 0u;
-    }
+/* Camera::GetRay (Camera.cpp:108-117): pixel centre, direction not normalised. slot = sample * npix + pixel */
+__device__ __forceinline__ void camera_ray(const RenderConst& rc, int32_t slot, d3& o, d3& d) {
+    const int pix = slot % rc.npix;
+    const int i = pix % rc.width, j = pix / rc.width;
+    const d3 ps = rc.pixel00 + ((double)i) * rc.dU + ((double)j) * rc.dV;
+    o = rc.center;
+    d = ps - rc.center;
 }
+
+/* deferred warp-aggregated queue push: issue() starts one atomic per destination queue (the leader
+ * of a class is a lane of that class, so one register holds every leader's result), complete()
+ * finishes it an event later, when the atomic's round trip to L2 has long been paid */
+struct DeferredPush {
+    int32_t cls, slot, raw;
+    __device__ __forceinline__ void init() { cls = -1; slot = 0; raw = 0; }
+    template <int NQ>
+    __device__ __forceinline__ void issue(int32_t* const (&counters)[NQ], int c, int32_t s) {
+        cls = c;
+        slot = s;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            const unsigned mask = __ballot_sync(0xffffffffu, c == q);
+            if (mask != 0 && lane_id() == __ffs(mask) - 1) raw = atomicAdd(counters[q], __popc(mask));
+        }
+    }
+    template <int NQ>
+    __device__ __forceinline__ void complete(int32_t* const (&queues)[NQ]) {
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            const unsigned mask = __ballot_sync(0xffffffffu, cls == q);
+            if (mask != 0) {
+                const int32_t base = __shfl_sync(0xffffffffu, raw, __ffs(mask) - 1);
+                if (cls == q) queues[q][base + __popc(mask & ((1u << lane_id()) - 1u))] = slot;
+            }
+        }
+        cls = -1;
+    }
+};
 
 /* closest hit for every path in the bounce's queue (persistent warps with lane refill,
  * traverse_warp.cuh), then the terminal cases that need no BSDF, then one queue per material class
- * for the shade kernels */
+ * for the shade kernels. Bounce 0 generates its camera rays itself (no ray-generation pass). */
 struct ExtendPolicy {
     const DevScene& S;
     const uint8_t* __restrict__ prim_class;
@@ -182,53 +220,78 @@ struct ExtendPolicy {
     BounceCtrl* ctrl;
     const int32_t* __restrict__ queue;
     int bounce;
-    int32_t slot;
-    __device__ __forceinline__ bool load(int32_t qi, d3& o, d3& d, double& t0, double& t1) {
-        slot = bounce == 0 ? qi : queue[qi];
-        o = ld3(pb.rec[slot].o);
-        d = ld3(pb.rec[slot].d);
+    DeferredPush push;
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return bounce == 0 ? qi : queue[qi]; }
+    __device__ __forceinline__ void prefetch(int32_t slot) const {
+        if (bounce != 0) prefetch_l2(pb.rec + slot);
+    }
+    __device__ __forceinline__ bool load(int32_t slot, d3& o, d3& d, double& t0, double& t1) const {
+        if (bounce == 0) {
+            camera_ray(rc, slot, o, d);
+        } else {
+            o = ld3(pb.rec[slot].o);
+            d = ld3(pb.rec[slot].d);
+        }
         t0 = 0.0001; /* Camera.cpp:125 */
         t1 = (double)INFINITY;
         return true;
     }
-    __device__ __forceinline__ void retire(bool finished, int32_t, const Hit& h) {
+    __device__ __forceinline__ void flush() {
+        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2]};
+        push.complete(queues);
+    }
+    __device__ __forceinline__ void retire(bool finished, int32_t slot, const Hit& h) {
+        flush();
         int cls = -1;
         if (finished) {
+            PathRec* __restrict__ r = pb.rec + slot;
+            d3 L0 = mk3(0.0, 0.0, 0.0); /* bounce 0 initialises the radiance of every path */
             if (h.slot < 0) {
                 /* a primary miss returns the background (Camera.cpp:127); with NEE on, a scattered
                  * ray that misses adds nothing (Camera.cpp:187-196) */
                 const d3 bg = mk3(rc.background[0], rc.background[1], rc.background[2]);
-                if (bounce == 0) st3(pb.rec[slot].L, bg);
-                else if (!rc.sample_lights) st3(pb.rec[slot].L, ld3(pb.rec[slot].L) + ld3(pb.rec[slot].T) * bg);
+                if (bounce == 0) L0 = bg;
+                else if (!rc.sample_lights) st3(r->L, ld3(r->L) + ld3(r->T) * bg);
             } else {
                 const int32_t prim = S.slot_prim[h.slot];
                 const int c = prim_class[prim];
                 if (c == CLS_EMISSIVE) {
                     /* an emitter ends the path (Camera.cpp:129-132); with NEE on, a scattered ray may
                      * collect it only if the scattering material skipped light sampling (:191-195) */
-                    const bool take = bounce == 0 || !rc.sample_lights || (pb.rec[slot].flags & PRT_FLAG_PREV_SKIP);
+                    const bool take = bounce == 0 || !rc.sample_lights || (r->flags & PRT_FLAG_PREV_SKIP);
                     if (take) {
                         const DevMaterial* m = S.materials + S.shade[prim].material;
                         const d3 le = mk3(m->emission[0], m->emission[1], m->emission[2]);
-                        if (bounce == 0) st3(pb.rec[slot].L, le);
-                        else st3(pb.rec[slot].L, ld3(pb.rec[slot].L) + ld3(pb.rec[slot].T) * le);
+                        if (bounce == 0) L0 = le;
+                        else st3(r->L, ld3(r->L) + ld3(r->T) * le);
                     }
                 } else if (c < CLS_SHADED) {
-                    pb.rec[slot].hit_prim = prim;
-                    pb.rec[slot].hit[0] = h.t;
-                    pb.rec[slot].hit[1] = h.alpha;
-                    pb.rec[slot].hit[2] = h.beta;
+                    r->hit_prim = prim;
+                    r->hit[0] = h.t;
+                    r->hit[1] = h.alpha;
+                    r->hit[2] = h.beta;
+                    if (bounce == 0) {
+                        d3 o, d;
+                        camera_ray(rc, slot, o, d);
+                        st3(r->o, o);
+                        st3(r->d, d);
+                        st3(r->T, mk3(1.0, 1.0, 1.0));
+                        r->dim = 0u;
+                        r->flags = 0u;
+                    }
                     cls = c;
                 }
                 /* CLS_EMPTY: no NEE, Scatter returns false (Material.h:537-540): the path ends */
             }
+            if (bounce == 0) st3(r->L, L0);
         }
-#pragma unroll
-        for (int c = 0; c < CLS_SHADED; ++c) {
-            const int at = warp_push(&ctrl->n_mat[c], cls == c);
-            if (at >= 0) pb.q_mat[c][at] = slot;
-        }
+        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2]};
+        push.issue(counters, cls, slot);
+#if !PRT_EXTEND_DEFER
+        flush();
+#endif
     }
+    __device__ __forceinline__ void finish() { flush(); }
 };
 
 template <bool COUNT>
@@ -236,28 +299,58 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScen
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = bounce == 0 ? rc.n_paths : ctrl->n_extend;
     VisitCounters cnt = {0, 0};
-    ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, pb.q_extend[bounce & 1], bounce, 0};
+    ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, pb.q_extend[bounce & 1], bounce, {-1, 0, 0}};
     traverse_persistent<false, COUNT>(S, pol, &ctrl->fetch_extend, n, cnt);
     flush_counters<COUNT>(cnt, pb.counters);
 }
 
-/* one path vertex of material class CLS (Camera.cpp:134-201) */
+/* one path vertex of material class CLS (Camera.cpp:134-201). Grid-stride over the class queue with
+ * the queue entry read two iterations ahead and the path record prefetched one iteration ahead (the
+ * chain queue -> record -> triangle -> material was 30 % of the stall samples, profiles/r1_s1_shade),
+ * and both output pushes deferred by one iteration. */
+#ifndef PRT_SHADE_MIN_BLOCKS
+#define PRT_SHADE_MIN_BLOCKS 4
+#endif
+#ifndef PRT_SHADE_PREFETCH
+#define PRT_SHADE_PREFETCH 1
+#endif
+#ifndef PRT_SHADE_DEFER
+#define PRT_SHADE_DEFER 0
+#endif
 template <int CLS>
-__global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
+__global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     BounceCtrl* next = pb.ctrl + bounce + 1;
     const int32_t n = ctrl->n_mat[CLS];
     const int32_t* __restrict__ queue = pb.q_mat[CLS];
-    int32_t* __restrict__ q_next = pb.q_extend[(bounce + 1) & 1];
+    int32_t* const out_q[2] = {pb.q_shadow, pb.q_extend[(bounce + 1) & 1]};
+    int32_t* const out_n[2] = {&ctrl->n_shadow, &next->n_extend};
     const int32_t n_round = (n + 31) & ~31;
-    for (int32_t qi = blockIdx.x * blockDim.x + threadIdx.x; qi < n_round; qi += gridDim.x * blockDim.x) {
+    const int32_t stride = gridDim.x * blockDim.x;
+    int32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
+    int32_t slot_next = qi < n ? queue[qi] : -1;
+    int32_t slot_next2 = qi + stride < n ? queue[qi + stride] : -1;
+    DeferredPush push_shadow, push_extend;
+    push_shadow.init();
+    push_extend.init();
+    for (; qi < n_round; qi += stride) {
         bool want_shadow = false, want_extend = false;
-        int32_t slot = 0;
-        if (qi < n) {
-            slot = queue[qi];
-            const int32_t prim = pb.rec[slot].hit_prim;
-            const double t = pb.rec[slot].hit[0], alpha = pb.rec[slot].hit[1], beta = pb.rec[slot].hit[2];
-            const d3 ro = ld3(pb.rec[slot].o), rd = ld3(pb.rec[slot].d);
+        const int32_t slot = slot_next;
+        slot_next = slot_next2;
+        slot_next2 = (int64_t)qi + 2 * (int64_t)stride < n ? queue[qi + 2 * stride] : -1;
+#if PRT_SHADE_PREFETCH
+        if (slot_next >= 0) {
+            prefetch_l2(pb.rec + slot_next);
+#if PRT_SHADE_PREFETCH > 1
+            prefetch_l2(reinterpret_cast<const char*>(pb.rec + slot_next) + 128);
+#endif
+        }
+#endif
+        if (slot >= 0) {
+            PathRec* __restrict__ r = pb.rec + slot;
+            const int32_t prim = r->hit_prim;
+            const double t = r->hit[0], alpha = r->hit[1], beta = r->hit[2];
+            const d3 ro = ld3(r->o), rd = ld3(r->d);
             const TriShade* __restrict__ sh = S.shade + prim;
             const DevMaterial m = S.materials[sh->material];
             /* the HitRecord of Triangle::Hit (Triangle.cpp:76-80,111) */
@@ -272,8 +365,8 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
 
             Rng rng;
             rng.seed = stream_seed(rc.rng_key, (uint32_t)(slot % rc.npix), (uint32_t)(rc.sample_first + slot / rc.npix));
-            rng.dim = pb.rec[slot].dim;
-            const d3 T = ld3(pb.rec[slot].T);
+            rng.dim = r->dim;
+            const d3 T = ld3(r->T);
 
             /* ---- next-event estimation (Camera.cpp:137-174) ---- */
             if (rc.sample_lights && !m.skip_light_sampling) {
@@ -292,9 +385,9 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
                     const double cos_theta = local_wi.z;
                     const double cos_theta_bar = dot(local_ln, -local_wi);
                     const d3 direct = emission * fr * cos_theta * cos_theta_bar / (distance * distance) / ls.pdf;
-                    st3(pb.rec[slot].sdir, light_dir);
-                    pb.rec[slot].sdist = distance;
-                    st3(pb.rec[slot].scontrib, T * direct);
+                    st3(r->sdir, light_dir);
+                    r->sdist = distance;
+                    st3(r->scontrib, T * direct);
                     want_shadow = true;
                 }
             }
@@ -306,21 +399,40 @@ __global__ void __launch_bounds__(128) k_shade(DevScene S, RenderConst rc, PathB
                 else scatter_mirror(s, wo, att, out_dir);
                 /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
                 if (bounce < rc.max_depth) {
-                    st3(pb.rec[slot].o, s.position);
-                    st3(pb.rec[slot].d, out_dir);
-                    st3(pb.rec[slot].T, T * att / rc.rr);
-                    pb.rec[slot].dim = rng.dim;
-                    pb.rec[slot].flags = m.skip_light_sampling ? PRT_FLAG_PREV_SKIP : 0u;
+                    st3(r->o, s.position);
+                    st3(r->d, out_dir);
+                    st3(r->T, T * att / rc.rr);
+                    r->dim = rng.dim;
+                    r->flags = m.skip_light_sampling ? PRT_FLAG_PREV_SKIP : 0u;
                     want_extend = true;
                 }
             }
-            if (want_shadow && !want_extend) st3(pb.rec[slot].o, s.position); /* shadow ray origin */
+            if (want_shadow && !want_extend) st3(r->o, s.position); /* shadow ray origin */
         }
         __syncwarp();
-        const int a = warp_push(&ctrl->n_shadow, want_shadow);
-        if (a >= 0) pb.q_shadow[a] = slot;
-        const int b = warp_push(&next->n_extend, want_extend);
-        if (b >= 0) q_next[b] = slot;
+        {
+            int32_t* const q0[1] = {out_q[0]};
+            int32_t* const q1[1] = {out_q[1]};
+            int32_t* const n0[1] = {out_n[0]};
+            int32_t* const n1[1] = {out_n[1]};
+#if PRT_SHADE_DEFER
+            push_shadow.complete(q0);
+            push_extend.complete(q1);
+            push_shadow.issue(n0, want_shadow ? 0 : -1, slot);
+            push_extend.issue(n1, want_extend ? 0 : -1, slot);
+#else
+            push_shadow.issue(n0, want_shadow ? 0 : -1, slot);
+            push_extend.issue(n1, want_extend ? 0 : -1, slot);
+            push_shadow.complete(q0);
+            push_extend.complete(q1);
+#endif
+        }
+    }
+    {
+        int32_t* const q0[1] = {out_q[0]};
+        int32_t* const q1[1] = {out_q[1]};
+        push_shadow.complete(q0);
+        push_extend.complete(q1);
     }
 }
 
@@ -332,12 +444,16 @@ template <bool EXACT>
 struct ShadowPolicy {
     const PathBuffers& pb;
     const int32_t* __restrict__ queue;
-    int32_t slot;
     d3 ps, dir;
     double distance;
-    __device__ __forceinline__ bool load(int32_t qi, d3& o, d3& d, double& t0, double& t1) {
-        slot = queue[qi];
-        /* by now pb.ray holds the hit position as the origin of the next segment */
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return queue[qi]; }
+    __device__ __forceinline__ void prefetch(int32_t slot) const {
+        prefetch_l2(pb.rec + slot);
+        prefetch_l2(reinterpret_cast<const char*>(pb.rec + slot) + 128);
+    }
+    __device__ __forceinline__ void finish() const {}
+    __device__ __forceinline__ bool load(int32_t slot, d3& o, d3& d, double& t0, double& t1) {
+        /* by now the record holds the hit position as the origin of the next segment */
         ps = ld3(pb.rec[slot].o);
         dir = ld3(pb.rec[slot].sdir);
         distance = pb.rec[slot].sdist;
@@ -347,7 +463,7 @@ struct ShadowPolicy {
         t1 = EXACT ? DBL_MAX : distance - 0.001;
         return true;
     }
-    __device__ __forceinline__ void retire(bool finished, int32_t, const Hit& h) {
+    __device__ __forceinline__ void retire(bool finished, int32_t slot, const Hit& h) {
         if (!finished) return;
         bool visible;
         if (EXACT) {
@@ -369,10 +485,10 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScen
     const int32_t n = ctrl->n_shadow;
     VisitCounters cnt = {0, 0};
     if (rc.flags & PRT_RENDER_EXACT_VISIBILITY) {
-        ShadowPolicy<true> pol = {pb, pb.q_shadow, 0, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
+        ShadowPolicy<true> pol = {pb, pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
         traverse_persistent<false, COUNT>(S, pol, &ctrl->fetch_shadow, n, cnt);
     } else {
-        ShadowPolicy<false> pol = {pb, pb.q_shadow, 0, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
+        ShadowPolicy<false> pol = {pb, pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
         traverse_persistent<true, COUNT>(S, pol, &ctrl->fetch_shadow, n, cnt);
     }
     flush_counters<COUNT>(cnt, pb.counters);
@@ -485,9 +601,6 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int g_shade0 = persistent_grid(k_shade<CLS_LAMBERT>, 128, shade_lc, rc.n_paths);
     const int g_shade1 = persistent_grid(k_shade<CLS_PHONG>, 128, shade_lc, rc.n_paths);
     const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR>, 128, shade_lc, rc.n_paths);
-    const int64_t rg = ((int64_t)rc.n_paths + 255) / 256;
-    k_raygen<<<(int)(rg < lc.sm_count * 8 ? rg : lc.sm_count * 8), 256, 0, st>>>(rc, pb);
-    ++launches;
     cudaEvent_t* ev = lc.stage_events;
     for (int b = 0; b < n_bounces; ++b) {
         if (ev) cudaEventRecord(ev[4 * b], st);

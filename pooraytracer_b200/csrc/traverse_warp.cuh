@@ -34,8 +34,17 @@ namespace prt {
 
 #define PRT_DONE 0x7fffffff      /* `cur` of a lane whose walk is over */
 #define PRT_BOX_EPS 4.76837158e-7f /* 2^-21 */
+#ifndef PRT_INNER_EXIT_BELOW
+#define PRT_INNER_EXIT_BELOW 8   /* leave the inner-node loop once fewer lanes than this are still descending */
+#endif
+#ifndef PRT_WALK_MODE
+#define PRT_WALK_MODE 0          /* 0: while-while, 1: gated if-if with a postponed leaf */
+#endif
+#ifndef PRT_LEAF_GATE
+#define PRT_LEAF_GATE 16         /* lanes that must hold a parked leaf before the triangle block runs */
+#endif
 #ifndef PRT_REFILL_BELOW
-#define PRT_REFILL_BELOW 24      /* refill idle lanes once fewer than this many lanes hold a ray */
+#define PRT_REFILL_BELOW 16      /* refill idle lanes once fewer than this many lanes hold a ray */
 #endif
 
 struct RayF32 { /* the FP32 side of a ray, for box tests only: t = b * inv - o * inv */
@@ -76,13 +85,44 @@ __device__ __forceinline__ bool box_f32(float lx, float ly, float lz, float hx, 
     return entry <= exit;
 }
 
+/* The reference-order walk is the rare path of the persistent kernels (boundary / equal-t hits):
+ * kept out of line so that its FP64 slab code and second stack do not weigh on the register
+ * allocation of the hot loop. */
+#ifndef PRT_REF_NOINLINE
+#define PRT_REF_NOINLINE 0
+#endif
+template <bool ANY, bool COUNT>
+#if PRT_REF_NOINLINE
+__device__ __noinline__
+#else
+__device__ __forceinline__
+#endif
+void trace_reference_cold(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, VisitCounters& cnt) {
+    trace_reference<ANY, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+}
+
+/* L2 prefetch of the line holding p (the record a lane will read once it is handed its ray) */
+#ifndef PRT_TRAV_PREFETCH
+#define PRT_TRAV_PREFETCH 0
+#endif
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 /*
  * The persistent loop. Policy P supplies the rays and consumes the results:
- *     bool P::load(int32_t qi, d3& o, d3& d, double& tmin, double& tmax)   per lane; false = skip
- *     void P::retire(bool finished, int32_t qi, const Hit& hit)            ALL lanes call it together;
- *                                                                          lanes with finished == true
- *                                                                          carry a completed ray
+ *     int32_t P::slot_of(int32_t qi)       queue entry qi -> the item ("slot") it names; per lane
+ *     void P::prefetch(int32_t slot)       optional L2 prefetch of what load(slot) will read
+ *     bool P::load(int32_t slot, d3& o, d3& d, double& tmin, double& tmax)   per lane; false = skip
+ *     void P::retire(bool finished, int32_t slot, const Hit& hit)   ALL lanes call it together;
+ *                                          lanes with finished == true carry a completed ray
+ *     void P::finish()                     ALL lanes, once, after the last retire
  * `cursor` is the queue's fetch counter (zeroed by the host), `n` the queue length.
+ *
+ * Work fetch is a three-stage pipeline per warp, so that neither the atomic on the cursor nor the
+ * queue read nor the DRAM latency of a ray record is waited for (ncu, profiles/r1_s1_extend: 30 %
+ * of the stall samples of the first persistent version sat on exactly those three):
+ *     chunk A   atomicAdd(cursor, 32) issued by lane 0, result not looked at yet
+ *     chunk B   base known; lane j has read slot_of(base + j); records prefetched one event later
+ *     chunk C   the chunk being handed out to lanes that run dry
  * Results are the reference's (see traverse.cuh): boundary and equal-t hits go through
  * trace_reference before they are retired.
  */
@@ -90,10 +130,12 @@ template <bool ANY, bool COUNT, class P>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, int32_t* cursor, int32_t n, VisitCounters& cnt) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
     int32_t stack[PRT_STACK];
     int sp = 0;
     int32_t cur = PRT_DONE;
-    int32_t qi = -1;
+    int32_t leaf = -1; /* PRT_WALK_MODE 1: parked leaf, (slot << 3) | (triangles left - 1) */
+    int32_t slot = -1;
     bool has_ray = false, exhausted = false, recheck = false;
     d3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
     double tmin = 0.0, tmax = 0.0, tbest = 0.0;
@@ -103,46 +145,74 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
     const bool use_sah = S.nodes2 != nullptr;
 
+    /* fetch pipeline state (c_*, b_base, b_pref are warp-uniform) */
+    int32_t a_raw = 0;                 /* lane 0: chunk A's atomic result */
+    int32_t b_base, b_slot;            /* chunk B */
+    bool b_pref = false;
+    int32_t c_slot = -1, c_off = 0, c_left = 0;
+    if (lane == 0) a_raw = atomicAdd(cursor, 32);
+    b_base = __shfl_sync(FULL, a_raw, 0);
+    b_slot = b_base + lane < n ? pol.slot_of(b_base + lane) : -1;
+    if (lane == 0) a_raw = atomicAdd(cursor, 32);
+
     for (;;) {
         /* ---- retire finished lanes, refill idle ones ---- */
-        const bool finished = has_ray && cur == PRT_DONE;
+        const bool finished = has_ray && cur == PRT_DONE && leaf < 0;
         if (finished) {
-            if (use_sah && recheck) {
-                if (ANY) trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-                else trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-            }
+            if (recheck) trace_reference_cold<ANY, COUNT>(S, o, d, tmin, tmax, hit, cnt);
             has_ray = false;
         }
         __syncwarp();
-        pol.retire(finished, qi, hit);
+        pol.retire(finished, slot, hit);
         if (!exhausted) {
             const unsigned need = __ballot_sync(FULL, !has_ray);
-            int32_t base = 0;
-            const int leader = __ffs(need) - 1;
-            if (lane == leader) base = atomicAdd(cursor, __popc(need));
-            base = __shfl_sync(FULL, base, leader);
-            if (base + __popc(need) >= n) exhausted = true; /* nothing left after this batch */
-            if (!has_ray) {
-                const int32_t mine = base + __popc(need & ((1u << lane) - 1u));
-                if (mine < n) {
-                    qi = mine;
-                    if (pol.load(qi, o, d, tmin, tmax)) {
-                        has_ray = true;
-                        recheck = false;
-                        hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
-                        tbest = tmax;
-                        sp = 0;
-                        if (use_sah) {
-                            rf = make_ray_f32(o, d);
-                            tmin32 = __double2float_rd(tmin);
-                            tbest32 = __double2float_ru(tbest);
-                            cur = S.n_tris > 0 ? 0 : PRT_DONE;
-                        } else {
-                            /* PRT_ACCEL_REFERENCE_BVH2: the reference's own walk, one ray per lane */
-                            if (ANY) trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-                            else trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-                            cur = PRT_DONE;
-                        }
+            int k = __popc(need);
+            int rank = __popc(need & lt_mask);
+            int32_t mine = -1;
+#pragma unroll 1
+            for (int round = 0; round < 2 && k > 0; ++round) {
+                if (c_left == 0) {
+                    /* C <- B, B <- A, issue a new A */
+                    if (b_base >= n) { exhausted = true; break; }
+                    c_slot = b_slot;
+                    c_off = 0;
+                    c_left = n - b_base < 32 ? n - b_base : 32;
+                    if (PRT_TRAV_PREFETCH && !b_pref && c_slot >= 0) pol.prefetch(c_slot);
+                    b_base = __shfl_sync(FULL, a_raw, 0);
+                    b_slot = b_base + lane < n ? pol.slot_of(b_base + lane) : -1;
+                    b_pref = false;
+                    if (lane == 0) a_raw = atomicAdd(cursor, 32);
+                }
+                const int take = k < c_left ? k : c_left;
+                const int32_t got = __shfl_sync(FULL, c_slot, (c_off + rank) & 31);
+                if (!has_ray && mine < 0 && rank >= 0 && rank < take) mine = got;
+                rank -= take;
+                k -= take;
+                c_off += take;
+                c_left -= take;
+            }
+            if (!b_pref && !exhausted) {
+                if (PRT_TRAV_PREFETCH && b_slot >= 0) pol.prefetch(b_slot);
+                b_pref = true;
+            }
+            if (mine >= 0) {
+                slot = mine;
+                if (pol.load(slot, o, d, tmin, tmax)) {
+                    has_ray = true;
+                    recheck = false;
+                    hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
+                    tbest = tmax;
+                    sp = 0;
+                    if (use_sah) {
+                        rf = make_ray_f32(o, d);
+                        tmin32 = __double2float_rd(tmin);
+                        tbest32 = __double2float_ru(tbest);
+                        cur = S.n_tris > 0 ? 0 : PRT_DONE;
+                    } else {
+                        /* PRT_ACCEL_REFERENCE_BVH2: the reference's own walk, one ray per lane, run
+                         * by the retire step of the next round */
+                        recheck = true;
+                        cur = PRT_DONE;
                     }
                 }
             }
@@ -153,9 +223,14 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
         }
 
         /* ---- walk until enough lanes have run dry ---- */
+#if PRT_WALK_MODE == 1
+        /* Gated if-if with one postponed leaf. Every round: (1) lanes holding an inner node take one
+         * step; a lane that reaches a leaf parks it in `leaf` and carries on with its stack
+         * (speculatively: the parked leaf has not shrunk tbest yet); (2) once PRT_LEAF_GATE lanes hold
+         * a parked leaf (or nobody can step any more), those lanes test ONE triangle each. Neither
+         * block waits for the slowest lane of the other. */
         for (;;) {
-            /* inner nodes: descend until this lane holds a leaf or is done */
-            while (cur >= 0 && cur != PRT_DONE) {
+            if (cur >= 0 && cur != PRT_DONE) {
                 const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes2 + cur);
                 const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
                 const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
@@ -174,6 +249,72 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                 } else {
                     cur = sp > 0 ? stack[--sp] : PRT_DONE;
                 }
+            }
+            if (cur < 0 && leaf < 0) { /* park the leaf, go on with the stack */
+                leaf = ~cur;
+                cur = sp > 0 ? stack[--sp] : PRT_DONE;
+            }
+            const unsigned lm = __ballot_sync(FULL, leaf >= 0);
+            const unsigned im = __ballot_sync(FULL, cur >= 0 && cur != PRT_DONE);
+            if (lm != 0 && (__popc(lm) >= PRT_LEAF_GATE || im == 0)) {
+                if (leaf >= 0) {
+                    /* leaf = (slot << 3) | (triangles left - 1): test `slot`, then advance */
+                    const int32_t ts = leaf >> 3;
+                    leaf = (leaf & 7) ? leaf + 7 : -1;
+                    double t, al, be;
+                    if (COUNT) cnt.tris++;
+                    if (tri_test(S.tris + ts, o, d, tmin, tbest, t, al, be)) {
+                        if (ANY) {
+                            /* a boundary hit may be one the reference's boxes reject: keep looking
+                             * for an interior one, let the reference decide if none turns up */
+                            if (on_boundary(al, be)) {
+                                recheck = true;
+                            } else {
+                                hit.slot = ts; hit.t = t; hit.alpha = al; hit.beta = be;
+                                recheck = false;
+                                leaf = -1; cur = PRT_DONE; sp = 0;
+                            }
+                        } else {
+                            recheck = hit.slot >= 0 && t == tbest; /* same t, another triangle */
+                            hit.slot = ts; hit.t = t; hit.alpha = al; hit.beta = be;
+                            tbest = t;
+                            tbest32 = __double2float_ru(t);
+                        }
+                    }
+                }
+            }
+            const unsigned walking = __ballot_sync(FULL, has_ray && !(cur == PRT_DONE && leaf < 0));
+            if (walking == 0) break;
+            if (!exhausted && __popc(walking) < PRT_REFILL_BELOW) break;
+        }
+        if (!ANY && has_ray && cur == PRT_DONE && leaf < 0 && hit.slot >= 0 && on_boundary(hit.alpha, hit.beta)) recheck = true;
+#else
+        for (;;) {
+            /* inner nodes: all lanes step together until fewer than PRT_INNER_EXIT_BELOW lanes still
+             * hold an inner node (the others hold a leaf or are done); stragglers wait through
+             * the leaf phase and carry on in the next round */
+            for (;;) {
+                if (cur >= 0 && cur != PRT_DONE) {
+                    const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes2 + cur);
+                    const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+                    const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
+                    if (COUNT) cnt.nodes++;
+                    float e0, e1;
+                    const bool h0 = box_f32(a.x, a.y, a.z, a.w, b.x, b.y, rf, tmin32, tbest32, e0);
+                    const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
+                    if (h0 && h1) {
+                        const bool swap = e1 < e0;
+                        if (sp < PRT_STACK) stack[sp++] = swap ? ch.x : ch.y;
+                        cur = swap ? ch.y : ch.x;
+                    } else if (h0) {
+                        cur = ch.x;
+                    } else if (h1) {
+                        cur = ch.y;
+                    } else {
+                        cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                    }
+                }
+                if (__popc(__ballot_sync(FULL, cur >= 0 && cur != PRT_DONE)) < PRT_INNER_EXIT_BELOW) break;
             }
             /* leaves */
             if (cur < 0) {
@@ -206,7 +347,9 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
             if (walking == 0) break;
             if (!exhausted && __popc(walking) < PRT_REFILL_BELOW) break;
         }
+#endif
     }
+    pol.finish();
 }
 
 }  // namespace prt
