@@ -66,6 +66,11 @@ typedef struct orc_render_info {
                              const double* normal, const double* tangent, const double* uv,        \
                              const double* u, int32_t n_u, double* attenuation, double* out_dir,   \
                              int32_t* n_draws, int32_t* scattered);                                \
+    /* Material::Eval as the NEE estimator calls it (Camera.cpp:160-168): context.wo =               */\
+    /* WorldToLocal(-ray_dir), localWi = WorldToLocal(wi_world) -> f[3]                              */\
+    int P##_material_eval(void* scene, int32_t material, const double* ray_dir,                    \
+                          const double* normal, const double* tangent, const double* uv,           \
+                          const double* wi_world, const double* u, int32_t n_u, double* f);        \
     int P##_texture_value(void* scene, int32_t texture, int64_t n, const double* uv, double* rgb); \
     /* camera ray of pixel (i,j): origin[3], direction[3] (Camera.cpp:108-117) */                  \
     int P##_camera_ray(const prt_camera* cam, int32_t i, int32_t j, double* origin, double* dir);

@@ -199,6 +199,8 @@ struct Mat {
     int type = PRT_MAT_LAMBERTIAN;
     V3 kd{0, 0, 0}, ks{0, 0, 0}, emission{0, 0, 0};
     double ns = 0, pkd = 1, pks = 0;
+    double alphaX = 0.3, alphaY = 0.3;  // CookTorrance, Material.h:370,518
+    V3 eta{1, 1, 1}, k{0, 0, 0};
     int kd_tex = -1;
     bool HasEmission() const { return type == PRT_MAT_DIFFUSE_LIGHT || type == PRT_MAT_DEBUG; }  // Material.h:166,528
     bool SkipLightSampling() const {  // Material.h:73,328,365,539
@@ -446,6 +448,116 @@ V3 tex_or_color(const Scene& s, int tex, V3 c, V2 uv) {
     return c;
 }
 
+
+/* ---------------------------------------------------------------------------------------------
+ * CookTorrance (Source/Material.h:368-521) and its helpers (Source/MaterialUtils.h)
+ * ------------------------------------------------------------------------------------------- */
+struct Cx { double re, im; };  // MaterialUtils.h:7-43 (Complex<double>)
+inline Cx cx(double re) { return {re, 0}; }
+inline Cx operator+(Cx a, Cx b) { return {a.re + b.re, a.im + b.im}; }
+inline Cx operator-(Cx a, Cx b) { return {a.re - b.re, a.im - b.im}; }
+inline Cx operator*(Cx a, Cx b) { return {a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re}; }
+inline Cx operator/(Cx a, Cx z) {
+    double scale = 1 / (z.re * z.re + z.im * z.im);
+    return {scale * (a.re * z.re + a.im * z.im), scale * (a.im * z.re - a.re * z.im)};
+}
+inline double Norm(Cx z) { return z.re * z.re + z.im * z.im; }  // MaterialUtils.h:45-48
+inline Cx CxSqrt(Cx z) {                                        // MaterialUtils.h:53-65
+    double n = std::sqrt(Norm(z)), t1 = std::sqrt(.5 * (n + std::fabs(z.re))), t2 = .5 * z.im / t1;
+    if (n == 0) return cx(0);
+    if (z.re >= 0) return {t1, t2};
+    return {std::fabs(t2), std::copysign(t1, z.im)};
+}
+inline double Clamp(double v, double lo, double hi) { return v < lo ? lo : (v > hi ? hi : v); }  // :67-71
+inline double Sqr(double v) { return v * v; }
+inline double Cos2Theta(V3 w) { return Sqr(w.z); }                               // :75-91
+inline double Sin2Theta(V3 w) { return std::max<double>(0., 1 - Cos2Theta(w)); }
+inline double Tan2Theta(V3 w) { return Sin2Theta(w) / Cos2Theta(w); }
+inline double SinTheta(V3 w) { return std::sqrt(Sin2Theta(w)); }
+inline double AbsCosTheta(V3 w) { return std::abs(w.z); }
+inline double CosPhi(V3 w) { double st = SinTheta(w); return (st == 0) ? 1 : Clamp(w.x / st, -1, 1); }
+inline double SinPhi(V3 w) { double st = SinTheta(w); return (st == 0) ? 0 : Clamp(w.y / st, -1, 1); }
+inline double AbsDot(V3 a, V3 b) { return std::fabs(dot(a, b)); }
+inline double Lerp(double x, double a, double b) { return (1 - x) * a + x * b; }
+inline double LengthSquared3(V3 v) { return Sqr(v.x) + Sqr(v.y) + Sqr(v.z); }
+inline double LengthSquared2(V2 v) { return Sqr(v.x) + Sqr(v.y); }
+inline bool SameHemisphere(V3 w, V3 wp) { return w.z * wp.z > 0; }                // :112-114
+inline double FrComplex(double cosTheta_i, Cx eta) {                             // :98-110
+    cosTheta_i = Clamp(cosTheta_i, 0, 1);
+    double sin2Theta_i = 1 - Sqr(cosTheta_i);
+    Cx sin2Theta_t = cx(sin2Theta_i) / (eta * eta);
+    Cx cosTheta_t = CxSqrt(cx(1) - sin2Theta_t);
+    Cx r_parl = (eta * cx(cosTheta_i) - cosTheta_t) / (eta * cx(cosTheta_i) + cosTheta_t);
+    Cx r_perp = (cx(cosTheta_i) - eta * cosTheta_t) / (cx(cosTheta_i) + eta * cosTheta_t);
+    return (Norm(r_parl) + Norm(r_perp)) / 2;
+}
+struct CookTorrance {
+    double alphaX, alphaY;
+    V3 eta, k;
+    double D(V3 wm) const {  // Material.h:374-381
+        double tan2Theta = Tan2Theta(wm);
+        if (std::isinf(tan2Theta)) return 0;
+        double cos4Theta = Sqr(Cos2Theta(wm));
+        double e = tan2Theta * (Sqr(CosPhi(wm) / alphaX) + Sqr(SinPhi(wm) / alphaY));
+        return 1 / (Pi * alphaX * alphaY * cos4Theta * Sqr(1 + e));
+    }
+    double Lambda(V3 w) const {  // :382-387
+        double tan2Theta = Tan2Theta(w);
+        if (std::isinf(tan2Theta)) return 0;
+        double alpha2 = Sqr(CosPhi(w) * alphaX) + Sqr(SinPhi(w) * alphaY);
+        return (std::sqrt(1 + alpha2 * tan2Theta) - 1) / 2;
+    }
+    double G1(V3 w) const { return 1 / (1 + Lambda(w)); }                       // :388
+    double G(V3 wo, V3 wi) const { return 1 / (1 + Lambda(wo) + Lambda(wi)); }  // :389-391
+    double Dw(V3 w, V3 wm) const { return G1(w) / AbsCosTheta(w) * D(wm) * AbsDot(w, wm); }  // :392-398
+    V3 Fresnel(V3 wo, V3 wm) const {  // :452,477
+        double c = AbsDot(wo, wm);
+        return v3(FrComplex(c, Cx{eta.x, k.x}), FrComplex(AbsDot(wo, wm), Cx{eta.y, k.y}), FrComplex(AbsDot(wo, wm), Cx{eta.z, k.z}));
+    }
+    V3 SampleWm(V3 w, V2 u) const {  // :410-430
+        V3 wh = normalize(v3(alphaX * w.x, alphaY * w.y, w.z));
+        if (wh.z < 0) wh = -wh;
+        V3 T1 = (wh.z < 0.99999) ? normalize(cross(v3(0., 0., 1.), wh)) : v3(1, 0, 0);
+        V3 T2 = cross(wh, T1);
+        // SampleUniformDiskPolar, RandomNumberGenerator.h:69-73
+        double r = std::sqrt(u.x);
+        double theta = 2 * Pi * u.y;
+        V2 p{r * std::cos(theta), r * std::sin(theta)};
+        double h = std::sqrt(1 - Sqr(p.x));
+        p.y = Lerp((1 + wh.z) / 2, h, p.y);
+        double pz = std::sqrt(std::max<double>(0., 1. - LengthSquared2(p)));
+        V3 nh = p.x * T1 + p.y * T2 + pz * wh;
+        return normalize(v3(alphaX * nh.x, alphaY * nh.y, std::max<double>(1e-6, nh.z)));
+    }
+    V3 Eval(V3 wi, V3 wo) const {  // :464-484
+        if (!SameHemisphere(wo, wi)) return v3(0, 0, 0);
+        double cosTheta_o = AbsCosTheta(wo), cosTheta_i = AbsCosTheta(wi);
+        if (cosTheta_i == 0 || cosTheta_o == 0) return v3(0, 0, 0);
+        V3 wm = wi + wo;
+        if (LengthSquared3(wm) == 0) return v3(0, 0, 0);
+        wm = normalize(wm);
+        V3 F = Fresnel(wo, wm);
+        return D(wm) * F * G(wo, wi) / (4 * cosTheta_i * cosTheta_o);
+    }
+    // Sample, :432-462. false = SampleFlags::Unset
+    bool Sample(V3 wo, Rng& rng, V3& wi, V3& f, double& pdf) const {
+        if (wo.z == 0) return false;
+        // vec2(RandomDouble(), RandomDouble()): arguments evaluated right to left by g++
+        double second_arg = rng.RandomDouble();
+        double first_arg = rng.RandomDouble();
+        V3 wm = SampleWm(wo, V2{first_arg, second_arg});
+        wi = Reflect(wo, wm);
+        if (!SameHemisphere(wo, wi)) return false;
+        pdf = Dw(wo, wm) / (4. * AbsDot(wo, wm));
+        double cosTheta_o = AbsCosTheta(wo), cosTheta_i = AbsCosTheta(wi);
+        if (cosTheta_i == 0 || cosTheta_o == 0) return false;
+        V3 F = Fresnel(wo, wm);
+        f = D(wm) * F * G(wo, wi) / (4. * cosTheta_i * cosTheta_o);
+        return true;
+    }
+};
+inline CookTorrance cook(const Mat& m) { return CookTorrance{m.alphaX, m.alphaY, m.eta, m.k}; }
+
 // Material::Eval for the NEE estimator (Camera.cpp:168)
 V3 mat_eval(const Scene& s, const Mat& m, V3 wi, const EvalCtx& c, Rng& rng) {
     switch (m.type) {
@@ -468,6 +580,8 @@ V3 mat_eval(const Scene& s, const Mat& m, V3 wi, const EvalCtx& c, Rng& rng) {
             }
             return v3(0, 0, 0);
         }
+        case PRT_MAT_COOK_TORRANCE:  // Material.h:464-484
+            return cook(m).Eval(wi, c.wo);
         default:
             return v3(0, 0, 0);  // Material.h:65-67 (Mirror, Empty, lights never reach Eval anyway)
     }
@@ -527,6 +641,14 @@ bool mat_scatter(const Scene& s, const Mat& m, V3 rayDir, const HitRec& rec, V3&
             V3 f = v3(1.0, 1.0, 1.0) / cosTheta;
             outDir = LocalToWorld(wi, c);
             att = f * cosTheta / 1.0;
+            return true;
+        }
+        case PRT_MAT_COOK_TORRANCE: {  // Material.h:485-509; wo is normalised here and only here
+            V3 wo = normalize(c.wo), wi, f;
+            double pdf;
+            if (!cook(m).Sample(wo, rng, wi, f, pdf)) return false;
+            att = f * wi.z / pdf;
+            outDir = LocalToWorld(wi, c);
             return true;
         }
         default:
@@ -693,6 +815,9 @@ int orc_scene_create(const prt_scene_desc* d, const char* const* texture_paths, 
         m.ks = v3(pm.ks[0], pm.ks[1], pm.ks[2]);
         m.emission = v3(pm.emission[0], pm.emission[1], pm.emission[2]);
         m.ns = pm.ns;
+        m.alphaX = pm.alpha_x; m.alphaY = pm.alpha_y;
+        m.eta = v3(pm.eta[0], pm.eta[1], pm.eta[2]);
+        m.k = v3(pm.k[0], pm.k[1], pm.k[2]);
         m.kd_tex = (pm.kd_tex >= 0 && pm.kd_tex < d->n_textures) ? pm.kd_tex : -1;
         if (m.ns <= 9.) { m.pkd = 1.0; m.pks = 0.0; } else { m.pkd = 0.6; m.pks = 0.4; }  // Material.h:318-327
         s->mats.push_back(m);
@@ -896,6 +1021,32 @@ int orc_material_scatter(void* p, int32_t material, const double* ray_dir, const
     out_dir[0] = od.x; out_dir[1] = od.y; out_dir[2] = od.z;
     *n_draws = rng.script_i;
     *scattered = ok ? 1 : 0;
+    return 0;
+}
+
+int orc_material_eval(void* p, int32_t material, const double* ray_dir, const double* normal,
+                      const double* tangent, const double* uv, const double* wi_world, const double* u, int32_t n_u,
+                      double* f) {
+    Scene* s = (Scene*)p;
+    if (!s || material < 0 || (size_t)material >= s->mats.size()) return PRT_ERR_INVALID_ARGUMENT;
+    std::vector<int32_t> script((size_t)n_u);
+    for (int i = 0; i < n_u; ++i) script[(size_t)i] = (int32_t)(u[i] * 2147483648.0);
+    Rng rng;
+    rng.script = script.data(); rng.script_n = n_u;
+    HitRec rec;
+    rec.position = v3(0, 0, 0);
+    rec.time = 1.0;
+    rec.tangent = v3(tangent[0], tangent[1], tangent[2]);
+    rec.uv = V2{uv[0], uv[1]};
+    rec.mat = material;
+    V3 rd = v3(ray_dir[0], ray_dir[1], ray_dir[2]);
+    rec.SetFaceNormal(rd, v3(normal[0], normal[1], normal[2]));
+    EvalCtx c;  // Camera.cpp:160-165
+    c.p = rec.position; c.uv = rec.uv; c.n = rec.normal; c.dpdus = rec.tangent;
+    c.wo = WorldToLocal(-rd, rec);
+    V3 localWi = WorldToLocal(v3(wi_world[0], wi_world[1], wi_world[2]), rec);
+    V3 fr = mat_eval(*s, s->mats[(size_t)material], localWi, c, rng);
+    f[0] = fr.x; f[1] = fr.y; f[2] = fr.z;
     return 0;
 }
 

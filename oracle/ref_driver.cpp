@@ -559,6 +559,37 @@ int ref_material_scatter(void* p, int32_t material, const double* ray_dir, const
     return 0;
 }
 
+int ref_material_eval(void* p, int32_t material, const double* ray_dir, const double* normal,
+                      const double* tangent, const double* uv, const double* wi_world, const double* u, int32_t n_u,
+                      double* f) {
+    RefScene* s = (RefScene*)p;
+    if (!s || material < 0 || (size_t)material >= s->materials.size()) return PRT_ERR_INVALID_ARGUMENT;
+    std::vector<int32_t> script((size_t)n_u);
+    for (int i = 0; i < n_u; ++i) script[(size_t)i] = (int32_t)(u[i] * 2147483648.0);
+    ThreadState& t = tls();
+    int saved = t.mode;
+    t.mode = MODE_SCRIPT; t.script = script.data(); t.script_n = n_u; t.script_i = 0;
+    HitRecord rec;
+    rec.position = vec3(0., 0., 0.);
+    rec.time = 1.0;
+    rec.tangent = vec3(tangent[0], tangent[1], tangent[2]);
+    rec.uv = vec2(uv[0], uv[1]);
+    rec.material = s->materials[(size_t)material];
+    Ray in(vec3(-ray_dir[0], -ray_dir[1], -ray_dir[2]), vec3(ray_dir[0], ray_dir[1], ray_dir[2]));
+    rec.SetFaceNormal(in, vec3(normal[0], normal[1], normal[2]));  // Hittable.cpp:8-13
+    MaterialEvalContext context;                                  // Camera.cpp:160-165
+    context.p = rec.position;
+    context.uv = rec.uv;
+    context.n = rec.normal;
+    context.dpdus = rec.tangent;
+    context.wo = Material::WorldToLocal(-in.direction, rec);
+    const vec3 localWi = Material::WorldToLocal(vec3(wi_world[0], wi_world[1], wi_world[2]), rec);
+    vec3 fr = rec.material->Eval(localWi, context);
+    for (int i = 0; i < 3; ++i) f[i] = fr[i];
+    t.script = nullptr; t.script_n = 0; t.mode = saved;
+    return 0;
+}
+
 int ref_texture_value(void* p, int32_t texture, int64_t n, const double* uv, double* rgb) {
     RefScene* s = (RefScene*)p;
     if (!s || texture < 0 || (size_t)texture >= s->textures.size()) return PRT_ERR_INVALID_ARGUMENT;

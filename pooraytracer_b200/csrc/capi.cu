@@ -92,6 +92,7 @@ struct prt_scene {
     DevBuf<uint8_t> d_texels;
     DevBuf<double> d_srgb;
     DevBuf<uint8_t> d_prim_class;
+    bool has_cook = false;
     DevScene dev;
 
     /* scratch for the host-pointer entry points */
@@ -106,7 +107,7 @@ struct prt_scene {
 
     /* wavefront pool */
     DevBuf<PathRec> p_rec;
-    DevBuf<int32_t> p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qs;
+    DevBuf<int32_t> p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qm3, p_qs;
     DevBuf<BounceCtrl> p_ctrl;
     int64_t pool_cap = 0;
     int pool_bounces = 0;
@@ -160,6 +161,7 @@ int ensure_pool(prt_scene* s, int64_t cap, int n_bounces) {
         CUDA_TRY(s->p_qm0.ensure((size_t)cap));
         CUDA_TRY(s->p_qm1.ensure((size_t)cap));
         CUDA_TRY(s->p_qm2.ensure((size_t)cap));
+        CUDA_TRY(s->p_qm3.ensure((size_t)cap));
         CUDA_TRY(s->p_qs.ensure((size_t)cap));
         s->pool_cap = cap;
     }
@@ -175,7 +177,7 @@ PathBuffers path_buffers(prt_scene* s) {
     pb.cap = s->pool_cap;
     pb.rec = s->p_rec.p;
     pb.q_extend[0] = s->p_q0.p; pb.q_extend[1] = s->p_q1.p;
-    pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p;
+    pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p; pb.q_mat[3] = s->p_qm3.p;
     pb.q_shadow = s->p_qs.p;
     pb.ctrl = s->p_ctrl.p;
     pb.counters = s->count_visits ? s->d_counters.p : nullptr;
@@ -286,9 +288,6 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     const int accel = opts ? opts->accel : PRT_ACCEL_SAH_BVH2;
     if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2) return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
     HostScene& h = s->host;
-    for (size_t m = 0; m < h.mesh_material.size(); ++m)
-        if (h.mesh_first[m + 1] > h.mesh_first[m] && h.materials[h.mesh_material[m]].type == PRT_MAT_COOK_TORRANCE)
-            return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: CookTorrance (Source/Material.h:368-521) is not implemented yet");
     try {
         int max_leaf = opts && opts->reserved[0] > 0 ? opts->reserved[0] : 4;
         if (accel == PRT_ACCEL_SAH_BVH2) h.build_sah_bvh2(default_host_threads(), max_leaf);
@@ -309,6 +308,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     CUDA_TRY(cudaSetDevice(s->ctx->device));
     cudaStream_t st = s->ctx->stream;
     std::vector<uint8_t> prim_class((size_t)h.n_tris);
+    s->has_cook = false;
     for (int64_t p = 0; p < h.n_tris; ++p) {
         const DevMaterial& m = h.dev_materials[h.shade[p].material];
         uint8_t c;
@@ -316,9 +316,11 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
         else if (m.type == PRT_MAT_LAMBERTIAN) c = CLS_LAMBERT;
         else if (m.type == PRT_MAT_PHONG) c = CLS_PHONG;
         else if (m.type == PRT_MAT_MIRROR) c = CLS_MIRROR;
+        else if (m.type == PRT_MAT_COOK_TORRANCE) c = CLS_COOK;
         else if (m.type == PRT_MAT_EMPTY) c = CLS_EMPTY;
         else c = CLS_LAMBERT; /* unknown types fall back to Lambertian like Model.cpp:282-285 */
         prim_class[p] = c;
+        if (c == CLS_COOK) s->has_cook = true;
     }
     std::vector<double> lut(h.srgb_lut, h.srgb_lut + 256);
     CUDA_TRY(s->d_tris.upload(h.isect_slots, st));
@@ -514,6 +516,7 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     if ((int64_t)rcn.width * rcn.height >= (int64_t(1) << 31) / 4) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_render: image too large");
     rcn.max_depth = params->max_depth;
     rcn.sample_lights = params->sample_lights ? 1 : 0;
+    rcn.has_cook = s->has_cook ? 1 : 0;
     rcn.flags = params->flags | (s->count_visits ? PRT_RENDER_COUNTERS : 0u);
     rcn.rr = params->russian_roulette;
     rcn.scale = 1.0 / params->samples_per_pixel;

@@ -74,6 +74,8 @@ struct alignas(16) DevMaterial {
     double ks[3];
     double emission[3]; /* GetEmission(): DiffuseLight radiance, or the albedo for DebugMaterial */
     double ns, pkd, pks;
+    double alpha_x, alpha_y; /* CookTorrance roughness (Material.h:518) */
+    double eta[3], k[3];     /* CookTorrance complex index of refraction per channel */
     int32_t type;
     int32_t kd_tex;
     int32_t has_emission;

@@ -29,6 +29,7 @@
 #include "launch.h"
 #include "rng.cuh"
 #include "shading.cuh"
+#include "cook_torrance.cuh"
 #include "traverse.cuh"
 #include "traverse_warp.cuh"
 
@@ -237,7 +238,7 @@ struct ExtendPolicy {
         return true;
     }
     __device__ __forceinline__ void flush() {
-        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2]};
+        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2], pb.q_mat[3]};
         push.complete(queues);
     }
     __device__ __forceinline__ void retire(bool finished, int32_t slot, const Hit& h) {
@@ -285,7 +286,7 @@ struct ExtendPolicy {
             }
             if (bounce == 0) st3(r->L, L0);
         }
-        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2]};
+        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2], &ctrl->n_mat[3]};
         push.issue(counters, cls, slot);
 #if !PRT_EXTEND_DEFER
         flush();
@@ -394,11 +395,13 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
             /* ---- Russian roulette + BSDF sampling (Camera.cpp:176-201) ---- */
             if (rng.next() < rc.rr) {
                 d3 att, out_dir;
+                bool scattered = true;
                 if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, out_dir);
                 else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, out_dir);
+                else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, out_dir);
                 else scatter_mirror(s, wo, att, out_dir);
                 /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
-                if (bounce < rc.max_depth) {
+                if (scattered && bounce < rc.max_depth) {
                     st3(r->o, s.position);
                     st3(r->d, out_dir);
                     st3(r->T, T * att / rc.rr);
@@ -601,6 +604,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int g_shade0 = persistent_grid(k_shade<CLS_LAMBERT>, 128, shade_lc, rc.n_paths);
     const int g_shade1 = persistent_grid(k_shade<CLS_PHONG>, 128, shade_lc, rc.n_paths);
     const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR>, 128, shade_lc, rc.n_paths);
+    const int g_shade3 = persistent_grid(k_shade<CLS_COOK>, 128, shade_lc, rc.n_paths);
     cudaEvent_t* ev = lc.stage_events;
     for (int b = 0; b < n_bounces; ++b) {
         if (ev) cudaEventRecord(ev[4 * b], st);
@@ -611,6 +615,10 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b);
         k_shade<CLS_MIRROR><<<g_shade2, 128, 0, st>>>(S, rc, pb, b);
         launches += 4;
+        if (rc.has_cook) {
+            k_shade<CLS_COOK><<<g_shade3, 128, 0, st>>>(S, rc, pb, b);
+            ++launches;
+        }
         if (ev) cudaEventRecord(ev[4 * b + 2], st);
         if (rc.sample_lights) {
             if (count) k_shadow<true><<<g_shadow, 128, 0, st>>>(S, rc, pb, b);

@@ -208,6 +208,8 @@ bool HostScene::ingest(const prt_scene_desc* d) {
         m.type = pm.type;
         m.kd_tex = (pm.kd_tex >= 0 && pm.kd_tex < d->n_textures) ? pm.kd_tex : -1;
         m.ns = pm.ns;
+        m.alpha_x = pm.alpha_x; m.alpha_y = pm.alpha_y;
+        for (int k = 0; k < 3; ++k) { m.eta[k] = pm.eta[k]; m.k[k] = pm.k[k]; }
         if (pm.ns <= 9.) { m.pkd = 1.0; m.pks = 0.0; } else { m.pkd = 0.6; m.pks = 0.4; } /* Material.h:318-327 */
         m.has_emission = (pm.type == PRT_MAT_DIFFUSE_LIGHT || pm.type == PRT_MAT_DEBUG) ? 1 : 0; /* :166,528 */
         for (int k = 0; k < 3; ++k) m.emission[k] = pm.type == PRT_MAT_DEBUG ? pm.kd[k] : (pm.type == PRT_MAT_DIFFUSE_LIGHT ? pm.emission[k] : 0.0);

@@ -141,7 +141,9 @@ __device__ __forceinline__ d3 reflect(d3 wo, d3 n) { return -wo + 2. * dot(wo, n
 
 /* ---- BSDFs ------------------------------------------------------------------------------------- */
 /* Material::Eval as the NEE estimator calls it (Camera.cpp:168); wi, wo in the local frame */
+__device__ __forceinline__ d3 cook_eval(const DevMaterial& m, d3 wi, d3 wo); /* cook_torrance.cuh */
 __device__ __forceinline__ d3 material_eval(const DevScene& S, const DevMaterial& m, d3 wi, d3 wo, d2 uv, const Rng& rng) {
+    if (m.type == PRT_MAT_COOK_TORRANCE) return cook_eval(m, wi, wo);
     if (m.type == PRT_MAT_LAMBERTIAN) return tex_or_color(S, m.kd_tex, m.kd, uv) * PRT_INV_PI;
     if (m.type == PRT_MAT_PHONG) {
         const double u = rng.peek();

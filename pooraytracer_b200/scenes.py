@@ -373,13 +373,22 @@ def tiny_scene(kind="mixed") -> SceneData:
     emp = b.material(Material("quad1", capi.MAT_EMPTY))
     light = b.material(Material("Light", capi.MAT_DIFFUSE_LIGHT, emission=(12.0, 11.0, 9.0)))
     light2 = b.material(Material("light1", capi.MAT_DIFFUSE_LIGHT, emission=(2.0, 3.0, 6.0)))
+    box_m, wall_m, ball_m = white, ph_s, ph_s
+    if kind == "cook":
+        # CookTorrance (Source/Material.h:368-521): the Au constants of Source/Model.cpp:309, an
+        # anisotropic Cu and a k = 0 dielectric-like Al2O3 (the commented-out alternatives there)
+        ball_m = b.material(Material("CookGold", capi.MAT_COOK_TORRANCE, kd=(0.8, 0.6, 0.2)))
+        wall_m = b.material(Material("CookCopper", capi.MAT_COOK_TORRANCE, kd=(0.7, 0.4, 0.3), alpha_x=0.1, alpha_y=0.5,
+                                     eta=(0.3, 0.7, 1.1), k=(4.4, 3.1, 2.5)))
+        box_m = b.material(Material("CookAlumina", capi.MAT_COOK_TORRANCE, kd=(0.9, 0.9, 0.9), alpha_x=0.6, alpha_y=0.05,
+                                    eta=(1.75, 1.76, 1.78), k=(0.0, 0.0, 0.0)))
     b.mesh("floor", texm, *grid((-1, 0, 1), (2, 0, 0), (0, 0, -2), 3, 3))
     b.mesh("ceiling", white, *quad((-1, 2, -1), (1, 2, -1), (1, 2, 1), (-1, 2, 1)))
     b.mesh("backWall", ph_d, *quad((-1, 0, -1), (1, 0, -1), (1, 2, -1), (-1, 2, -1)))
-    b.mesh("leftWall", ph_s, *quad((-1, 0, 1), (-1, 0, -1), (-1, 2, -1), (-1, 2, 1)))
+    b.mesh("leftWall", wall_m, *quad((-1, 0, 1), (-1, 0, -1), (-1, 2, -1), (-1, 2, 1)))
     b.mesh("rightWall", mir, *quad((1, 0, -1), (1, 0, 1), (1, 2, 1), (1, 2, -1)))
-    b.mesh("box", white, *box((-0.3, 0.35, -0.2), (0.3, 0.35, 0.3), rot_y_deg=25.0))
-    b.mesh("ball", ph_s, *uv_sphere((0.45, 0.3, 0.35), 0.3, 12, 6))
+    b.mesh("box", box_m, *box((-0.3, 0.35, -0.2), (0.3, 0.35, 0.3), rot_y_deg=25.0))
+    b.mesh("ball", ball_m, *uv_sphere((0.45, 0.3, 0.35), 0.3, 12, 6))
     b.mesh("pane", emp, *quad((-0.9, 0.2, 0.6), (-0.5, 0.2, 0.6), (-0.5, 0.6, 0.6), (-0.9, 0.6, 0.6)))
     b.mesh("light", light, *quad((-0.3, 1.98, -0.3), (0.3, 1.98, -0.3), (0.3, 1.98, 0.3), (-0.3, 1.98, 0.3)))
     b.mesh("light2", light2, *uv_sphere((-0.6, 1.4, -0.6), 0.12, 8, 4))

@@ -25,6 +25,10 @@ def bathroom_small():
     return scenes.bathroom_like(64, 36, detail=16)
 
 
+def cook():
+    return scenes.tiny_scene("cook")
+
+
 SCENES = {"tiny": tiny, "cornell": cornell_small, "veach": veach_small, "bathroom": bathroom_small}
 
 
@@ -109,6 +113,23 @@ def scatter_inputs(n=64, seed=6):
     return out
 
 
+def eval_inputs(n=64, seed=8):
+    """(ray_dir, normal, tangent, uv, wi_world, u[2]) tuples for Material::Eval as Camera::RayColor calls it
+    (unnormalised ray directions, unit light directions on either side of the surface)."""
+    r = hash_uniform(n * 8, seed, 5).reshape(n, 8)
+    out = []
+    for i, (rd, nrm, tng, uv, u) in enumerate(scatter_inputs(n, seed)):
+        wi = r[i, 0:3] * 2 - 1
+        wi /= np.linalg.norm(wi)
+        if i % 9 == 0:
+            wi = np.cross(nrm, tng)  # grazing: exactly in the tangent plane
+        out.append((rd, nrm, tng, uv, wi, u[:2]))
+    return out
+
+
+# scenes that only the render / material fixtures use (no ray fixtures)
+EXTRA_SCENES = {"cook": cook}
+
 RENDER_CASES = {
     # name: (scene key, width, height, spp, depth, sample_lights, rng_key, background)
     "tiny_nee": ("tiny", 48, 32, 4, 8, True, 5, (0.0, 0.0, 0.0)),
@@ -116,4 +137,10 @@ RENDER_CASES = {
     "cornell_nee": ("cornell", 40, 40, 2, 10, True, 1, (0.0, 0.0, 0.0)),
     "veach_nee": ("veach", 48, 27, 3, 12, True, 3, (0.0, 0.0, 0.0)),
     "bathroom_nee": ("bathroom", 48, 27, 2, 12, True, 7, (0.0, 0.0, 0.0)),
+    "cook_nee": ("cook", 48, 32, 4, 8, True, 13, (0.0, 0.0, 0.0)),
+    "cook_plain": ("cook", 24, 16, 3, 6, False, 17, (0.2, 0.3, 0.1)),
 }
+
+
+def scene_by_key(key):
+    return (SCENES.get(key) or EXTRA_SCENES[key])()

@@ -20,8 +20,49 @@ import oracle_lib as ol  # noqa: E402
 from pooraytracer_b200.api import make_camera, make_params  # noqa: E402
 
 
+def material_rows(R, sc):
+    """Scatter and Eval of every material with scripted uniforms -> (scatter rows, eval rows)"""
+    rows, erows = [], []
+    for mi in range(len(sc.materials)):
+        for (rd, nrm, tng, uv, u) in cases.scatter_inputs():
+            att, od, nd, ok = R.material_scatter(mi, rd, nrm, tng, uv, u)
+            rows.append(np.concatenate([[mi], att, od, [nd, float(ok)]]))
+        for (rd, nrm, tng, uv, wi, u) in cases.eval_inputs():
+            erows.append(np.concatenate([[mi], R.material_eval(mi, rd, nrm, tng, uv, wi, u)]))
+    return np.array(rows), np.array(erows)
+
+
+def render_fixture(name):
+    key, w, h, spp, depth, nee, rkey, bg = cases.RENDER_CASES[name]
+    sc = cases.scene_by_key(key)
+    R = ol.OracleScene("ref", sc, ol.DEFINE_UB)
+    cam = make_camera(sc.camera, w, h)
+    prm = make_params(spp, depth, sample_lights=nee, rng_key=rkey, background=bg)
+    img, info = R.render(cam, prm, ol.RNG_COUNTER, nthreads=8)
+    px = [(w // 2, h // 2), (3, 5), (w - 2, h - 3), (w // 3, 2 * h // 3)]
+    samples = np.stack([R.pixel_samples(cam, prm, x, y) for x, y in px])
+    np.savez_compressed(os.path.join(HERE, f"render_{name}.npz"), image=img, pixels=np.array(px), samples=samples,
+                        world_hit_calls=info.world_hit_calls, shadow_calls=info.shadow_calls)
+    print("render", name, img.shape, float(img.mean()), info.world_hit_calls)
+    R.close()
+
+
+def cook_fixtures():
+    """CookTorrance: Scatter / Eval with scripted uniforms + two renders"""
+    sc = cases.cook()
+    R = ol.OracleScene("ref", sc, ol.DEFINE_UB)
+    rows, erows = material_rows(R, sc)
+    np.savez_compressed(os.path.join(HERE, "material_cook.npz"), scatter=rows, eval=erows)
+    print("material_cook", rows.shape, erows.shape, "scattered", int(rows[:, -1].sum()), "eval nonzero", int((erows[:, 1:] != 0).any(1).sum()))
+    R.close()
+    for name in ("cook_nee", "cook_plain"):
+        render_fixture(name)
+
+
 def main():
     assert ol.available("ref"), "build oracle/_ref first (make -C oracle ref)"
+    if len(sys.argv) > 1 and sys.argv[1] == "cook":
+        return cook_fixtures()
     tag = ol.PER_TRIANGLE_MATERIAL | ol.UV_TAG
     for key, make in list(cases.SCENES.items()) + [("ties", cases.tie_scene)]:
         sc = make()
@@ -64,18 +105,10 @@ def main():
     np.savez_compressed(os.path.join(HERE, "texture_bathroom.npz"), uv=uv, **tex)
     R.close()
 
-    for name, (key, w, h, spp, depth, nee, rkey, bg) in cases.RENDER_CASES.items():
-        sc = cases.SCENES[key]()
-        R = ol.OracleScene("ref", sc, ol.DEFINE_UB)
-        cam = make_camera(sc.camera, w, h)
-        prm = make_params(spp, depth, sample_lights=nee, rng_key=rkey, background=bg)
-        img, info = R.render(cam, prm, ol.RNG_COUNTER, nthreads=8)
-        px = [(w // 2, h // 2), (3, 5), (w - 2, h - 3), (w // 3, 2 * h // 3)]
-        samples = np.stack([R.pixel_samples(cam, prm, x, y) for x, y in px])
-        np.savez_compressed(os.path.join(HERE, f"render_{name}.npz"), image=img, pixels=np.array(px), samples=samples,
-                            world_hit_calls=info.world_hit_calls, shadow_calls=info.shadow_calls)
-        print("render", name, img.shape, float(img.mean()), info.world_hit_calls)
-        R.close()
+    for name in cases.RENDER_CASES:
+        if not name.startswith("cook"):
+            render_fixture(name)
+    cook_fixtures()
 
 
 if __name__ == "__main__":

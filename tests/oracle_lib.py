@@ -166,6 +166,15 @@ class OracleScene:
         assert rc == 0, rc
         return att, od, nd.value, bool(sc.value)
 
+    def material_eval(self, material, ray_dir, normal, tangent, uv, wi_world, u):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        f = np.zeros(3)
+        c = lambda a: _ptr(np.ascontiguousarray(a, dtype=np.float64))  # noqa: E731
+        rc = self.o.fn("material_eval")(self.handle, C.c_int32(material), c(ray_dir), c(normal), c(tangent), c(uv), c(wi_world),
+                                        _ptr(u), C.c_int32(len(u)), _ptr(f))
+        assert rc == 0, rc
+        return f
+
     def texture_value(self, texture, uv):
         uv = np.ascontiguousarray(uv, dtype=np.float64).reshape(-1, 2)
         out = np.zeros((uv.shape[0], 3))

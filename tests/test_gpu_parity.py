@@ -128,7 +128,7 @@ def test_edge_cases(gpu_ctx):
 
 def _render_case(name):
     key, w, h, spp, depth, nee, rkey, bg = cases.RENDER_CASES[name]
-    sc = cases.SCENES[key]()
+    sc = cases.scene_by_key(key)
     cam = make_camera(sc.camera, w, h)
     prm = make_params(spp, depth, sample_lights=nee, rng_key=rkey, background=bg)
     return sc, cam, prm

@@ -83,6 +83,25 @@ def test_port_material_scatter_matches_reference_golden(built, flags, name):
         assert np.array_equal(rows, g, equal_nan=True)
 
 
+def test_port_cook_torrance_matches_reference_golden(built):
+    """SURVEY §8 a18: CookTorrance::Scatter / ::Eval (Material.h:368-521, MaterialUtils.h) with scripted
+    uniforms, every material of the `cook` scene, bit for bit"""
+    sc = cases.cook()
+    g = gold("material_cook.npz")
+    O = ol.OracleScene("orc", sc, ol.DEFINE_UB)
+    rows, erows = [], []
+    for mi in range(len(sc.materials)):
+        for (rd, nrm, tng, uv, u) in cases.scatter_inputs():
+            att, od, nd, ok = O.material_scatter(mi, rd, nrm, tng, uv, u)
+            rows.append(np.concatenate([[mi], att, od, [nd, float(ok)]]))
+        for (rd, nrm, tng, uv, wi, u) in cases.eval_inputs():
+            erows.append(np.concatenate([[mi], O.material_eval(mi, rd, nrm, tng, uv, wi, u)]))
+    assert np.array_equal(np.array(rows), g["scatter"], equal_nan=True)
+    assert np.array_equal(np.array(erows), g["eval"], equal_nan=True)
+    ct = [i for i, m in enumerate(sc.materials) if m.type == 3]
+    assert len(ct) == 3 and (g["scatter"][np.isin(g["scatter"][:, 0], ct), -1] == 1).sum() > 100
+
+
 def test_port_texture_matches_reference_golden(built):
     sc = cases.bathroom_small()
     g = gold("texture_bathroom.npz")
@@ -94,7 +113,7 @@ def test_port_texture_matches_reference_golden(built):
 @pytest.mark.parametrize("name", list(cases.RENDER_CASES))
 def test_port_render_matches_reference_golden(built, name):
     key, w, h, spp, depth, nee, rkey, bg = cases.RENDER_CASES[name]
-    sc = cases.SCENES[key]()
+    sc = cases.scene_by_key(key)
     g = gold(f"render_{name}.npz")
     O = ol.OracleScene("orc", sc, ol.DEFINE_UB)
     cam = make_camera(sc.camera, w, h)
