@@ -230,6 +230,50 @@ int prt_render_device(prt_scene* scene, const prt_camera* camera,
  * of the scrubbed linear image (the .hdr payload). Device buffer in, host buffers out. */
 int prt_resolve_device(prt_scene* scene, const double* rgb_device, int32_t width, int32_t height,
                        uint8_t* rgb8, float* rgb32f);
+/* Same with the radiance image in host memory (the colorAttachment a caller kept). */
+int prt_resolve(prt_scene* scene, const double* rgb, int32_t width, int32_t height, uint8_t* rgb8,
+                float* rgb32f);
+
+/* ---- scene files: replaces Model::Model + Camera::SetViewParametersByXmlFile -------------------
+ * Host-only (no GPU needed). Reads <dir>/<name>.obj, the .mtl it names, <dir>/<name>.xml (camera +
+ * <light mtlname radiance>), and the map_Kd images, the way Source/Model.cpp:53-394 and
+ * Source/Camera.cpp:339-389 do through tinyobjloader / tinyxml2 / stb_image:
+ *   - one mesh per OBJ shape (`g` / `o`), the material of the shape's FIRST face rules the whole
+ *     shape (Model.cpp:118), polygons are triangulated like tinyobjloader's default config;
+ *   - the material TYPE comes from the reference's name table (Model.cpp:16-51), unknown names are
+ *     Lambertian, a name in the table as Phong falls back to CreatePhoneReflectanceMaterial;
+ *   - DiffuseLight radiance comes from the XML's <light> elements (Model.cpp:320-347);
+ *   - triangles whose texture coordinates coincide get (0,0),(1,0),(1,1) (Model.cpp:170-175);
+ *   - anonymous `g` lines are named Group_<n> IN MEMORY (the reference rewrites the user's .obj
+ *     file in place, Model.cpp:195-268; this loader never writes to its inputs).
+ * PRT_LOAD_STRTOD parses reals with strtod (correctly rounded) instead of tinyobjloader's own
+ * digit-accumulating parser (the default, which is what the reference's numbers went through). */
+typedef struct prt_model prt_model;
+#define PRT_LOAD_STRTOD 1u
+int prt_model_load(const char* directory, const char* name, uint32_t flags, prt_model** out);
+void prt_model_destroy(prt_model* model);
+/* The loaded scene as flat arrays owned by the model (valid until prt_model_destroy). */
+const prt_scene_desc* prt_model_desc(const prt_model* model);
+/* Camera of the XML file (image size, fovy, eye, lookat, up); PRT_ERR_INVALID_ARGUMENT when the file
+ * has no <camera> element (the reference then renders with Camera.h's defaults). */
+int prt_model_camera(const prt_model* model, prt_camera* out);
+/* Names as the reference logs them (Model.cpp:121-125): shape name and material name of mesh m. */
+const char* prt_model_mesh_name(const prt_model* model, int32_t mesh);
+const char* prt_model_material_name(const prt_model* model, int32_t material);
+/* Warnings collected while loading (unsupported image formats, unknown materials ...), one per
+ * line; never NULL. */
+const char* prt_model_warnings(const prt_model* model);
+
+/* ---- image files: replaces stbi_write_png / stbi_write_hdr (Camera.cpp:302,327) and stbi_load ---
+ * PNG: 8-bit RGB, rows top to bottom. HDR: Radiance RGBE of float32 RGB (the float -> RGBE
+ * conversion is stb_image_write's: frexp of the largest component). */
+int prt_write_png(const char* path, int32_t width, int32_t height, const uint8_t* rgb8);
+int prt_write_hdr(const char* path, int32_t width, int32_t height, const float* rgb32f);
+/* Decodes a PNG (any colour type / bit depth, non-interlaced), BMP (24/32-bit) or binary PNM into
+ * `channels` interleaved u8 per texel the way stbi_load(path, .., 0) does. *texels is malloc'ed:
+ * release it with prt_image_free. */
+int prt_image_load(const char* path, int32_t* width, int32_t* height, int32_t* channels, uint8_t** texels);
+void prt_image_free(uint8_t* texels);
 
 /* enable != 0: the ray-query and render kernels count BVH node and triangle record fetches
  * (instrumented instantiations; slower). Read them back through prt_get_stats. */

@@ -30,6 +30,8 @@ RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
 RENDER_STAGE_TIMING = 4
 
+LOAD_STRTOD = 1
+
 c_double3 = C.c_double * 3
 
 
@@ -140,9 +142,21 @@ PROTOTYPES = {
     "prt_render": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p]),
     "prt_render_device": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p, C.c_void_p]),
     "prt_resolve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "prt_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "prt_set_counters": (C.c_int, [C.c_void_p, C.c_int]),
     "prt_get_stats": (C.c_int, [C.c_void_p, C.POINTER(PrtStats)]),
     "prt_synchronize": (C.c_int, [C.c_void_p]),
+    "prt_model_load": (C.c_int, [C.c_char_p, C.c_char_p, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "prt_model_destroy": (None, [C.c_void_p]),
+    "prt_model_desc": (C.POINTER(PrtSceneDesc), [C.c_void_p]),
+    "prt_model_camera": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera)]),
+    "prt_model_mesh_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "prt_model_material_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "prt_model_warnings": (C.c_char_p, [C.c_void_p]),
+    "prt_write_png": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "prt_write_hdr": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "prt_image_load": (C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]),
+    "prt_image_free": (None, [C.c_void_p]),
 }
 
 _lib = None

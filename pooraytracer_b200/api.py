@@ -126,14 +126,121 @@ class Context:
             pass
 
 
-class Scene:
-    def __init__(self, ctx: Context, data: SceneData, accel: int | None = capi.ACCEL_SAH_BVH2):
-        self.ctx, self.lib, self.data = ctx, ctx.lib, data
-        desc, keep = make_scene_desc(data)
+class Model:
+    """Scene files -> flat arrays: Model::Model + Camera::SetViewParametersByXmlFile
+    (Source/Model.cpp:53-394, Source/Camera.cpp:339-389) through prt_model_load."""
+
+    def __init__(self, directory: str, name: str, flags: int = 0):
+        self.lib = capi.load_library()
         h = C.c_void_p()
-        _check(self.lib, self.lib.prt_scene_create(ctx.handle, C.byref(desc), C.byref(h)))
+        _check(self.lib, self.lib.prt_model_load(directory.encode(), name.encode(), int(flags), C.byref(h)))
         self.handle = h
-        del keep
+        self.desc = self.lib.prt_model_desc(h).contents
+        self.n_triangles = int(self.desc.n_triangles)
+
+    def _array(self, ptr, shape, dtype):
+        n = int(np.prod(shape))
+        if not ptr or n == 0:
+            return np.zeros(shape, dtype=dtype)
+        buf = (C.c_char * (n * np.dtype(dtype).itemsize)).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape).copy()
+
+    @property
+    def vertices(self):
+        return self._array(self.desc.vertices, (self.n_triangles, 3, 3), np.float64)
+
+    @property
+    def normals(self):
+        return self._array(self.desc.normals, (self.n_triangles, 3, 3), np.float64)
+
+    @property
+    def texcoords(self):
+        return self._array(self.desc.texcoords, (self.n_triangles, 3, 2), np.float64)
+
+    @property
+    def mesh_first(self):
+        return self._array(self.desc.mesh_first, (self.desc.n_meshes + 1,), np.int64)
+
+    @property
+    def mesh_material(self):
+        return self._array(self.desc.mesh_material, (self.desc.n_meshes,), np.int32)
+
+    @property
+    def mesh_names(self):
+        return [self.lib.prt_model_mesh_name(self.handle, i).decode() for i in range(self.desc.n_meshes)]
+
+    @property
+    def material_names(self):
+        return [self.lib.prt_model_material_name(self.handle, i).decode() for i in range(self.desc.n_materials)]
+
+    @property
+    def materials(self):
+        return [capi.PrtMaterial.from_buffer_copy(self.desc.materials[i]) for i in range(self.desc.n_materials)]  # copies: outlive the model
+
+    def texture(self, i):
+        t = self.desc.textures[i]
+        if not t.texels:
+            return None
+        return self._array(t.texels, (t.height, t.width, t.channels), np.uint8)
+
+    @property
+    def warnings(self):
+        return [w for w in self.lib.prt_model_warnings(self.handle).decode("utf-8", "replace").split("\n") if w]
+
+    def camera(self) -> capi.PrtCamera:
+        c = capi.PrtCamera()
+        _check(self.lib, self.lib.prt_model_camera(self.handle, C.byref(c)))
+        return c
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.prt_model_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def write_png(path: str, rgb8: np.ndarray):
+    lib = capi.load_library()
+    a = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    _check(lib, lib.prt_write_png(path.encode(), a.shape[1], a.shape[0], _ptr(a)))
+
+
+def write_hdr(path: str, rgb32f: np.ndarray):
+    lib = capi.load_library()
+    a = np.ascontiguousarray(rgb32f, dtype=np.float32)
+    _check(lib, lib.prt_write_hdr(path.encode(), a.shape[1], a.shape[0], _ptr(a)))
+
+
+def load_image(path: str) -> np.ndarray:
+    """stbi_load(path, &w, &h, &c, 0) -> uint8 [h, w, c]"""
+    lib = capi.load_library()
+    w, h, c, px = C.c_int32(), C.c_int32(), C.c_int32(), C.c_void_p()
+    _check(lib, lib.prt_image_load(path.encode(), C.byref(w), C.byref(h), C.byref(c), C.byref(px)))
+    try:
+        n = w.value * h.value * c.value
+        out = np.frombuffer((C.c_char * n).from_address(px.value), dtype=np.uint8).reshape(h.value, w.value, c.value).copy()
+    finally:
+        lib.prt_image_free(px)
+    return out
+
+
+class Scene:
+    def __init__(self, ctx: Context, data, accel: int | None = capi.ACCEL_SAH_BVH2):
+        """data: a SceneData (procedural arrays) or a Model (loaded scene files)"""
+        self.ctx, self.lib, self.data = ctx, ctx.lib, data
+        h = C.c_void_p()
+        if isinstance(data, Model):
+            _check(self.lib, self.lib.prt_scene_create(ctx.handle, C.byref(data.desc), C.byref(h)))
+        else:
+            desc, keep = make_scene_desc(data)
+            _check(self.lib, self.lib.prt_scene_create(ctx.handle, C.byref(desc), C.byref(h)))
+            del keep
+        self.handle = h
         if accel is not None:
             self.commit(accel)
 

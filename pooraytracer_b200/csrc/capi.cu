@@ -28,6 +28,10 @@ int fail(int code, const std::string& msg) {
 }
 }  // namespace
 
+namespace prt {
+int set_error(int code, const std::string& msg) { return fail(code, msg); } /* for scene_io.cpp */
+}
+
 struct prt_context {
     int device = -1; /* < 0: host-only */
     cudaStream_t stream = nullptr;
@@ -609,6 +613,16 @@ int prt_resolve_device(prt_scene* s, const double* rgb_device, int32_t width, in
     if (rgb32f) CUDA_TRY(cudaMemcpyAsync(rgb32f, s->s_rgb32f.p, n * sizeof(float), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return PRT_OK;
+}
+
+int prt_resolve(prt_scene* s, const double* rgb, int32_t width, int32_t height, uint8_t* rgb8, float* rgb32f) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (!rgb || width < 1 || height < 1) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_resolve: bad argument");
+    const size_t n = (size_t)width * height * 3;
+    CUDA_TRY(s->s_rgb.ensure(n));
+    CUDA_TRY(cudaMemcpyAsync(s->s_rgb.p, rgb, n * sizeof(double), cudaMemcpyHostToDevice, s->ctx->stream));
+    return prt_resolve_device(s, s->s_rgb.p, width, height, rgb8, rgb32f);
 }
 
 int prt_get_stats(const prt_scene* cs, prt_stats* out) {

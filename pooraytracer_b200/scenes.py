@@ -456,3 +456,107 @@ def camera_rays(camera: dict, width=None, height=None):
     d = (p00 + i[..., None] * du + j[..., None] * dv - eye).reshape(-1, 3)
     o = np.broadcast_to(eye, d.shape).copy()
     return o, np.ascontiguousarray(d)
+
+
+# ------------------------------------------------------------------------------------------------
+# scene files (example-scenes-cg24 layout: <dir>/<name>.obj + .mtl + .xml + textures)
+# ------------------------------------------------------------------------------------------------
+def png_bytes(img: np.ndarray, filters=(0, 1, 2, 3, 4), level=6) -> bytes:
+    """PNG encoder for uint8 [H,W] / [H,W,C] (C = 1..4): real deflate (dynamic Huffman blocks) and a
+    per-row rotation through the five filter types, so that reading it back exercises all of a
+    decoder."""
+    import struct
+    import zlib
+    a = np.ascontiguousarray(img, dtype=np.uint8)
+    if a.ndim == 2:
+        a = a[:, :, None]
+    h, w, c = a.shape
+    ctype = {1: 0, 2: 4, 3: 2, 4: 6}[c]
+    rows = a.reshape(h, w * c).astype(np.int32)
+    raw = bytearray()
+    prev = np.zeros(w * c, dtype=np.int32)
+    for y in range(h):
+        cur = rows[y]
+        ft = filters[y % len(filters)]
+        left = np.concatenate([np.zeros(c, np.int32), cur[:-c]])
+        upleft = np.concatenate([np.zeros(c, np.int32), prev[:-c]])
+        if ft == 0:
+            out = cur
+        elif ft == 1:
+            out = cur - left
+        elif ft == 2:
+            out = cur - prev
+        elif ft == 3:
+            out = cur - ((left + prev) >> 1)
+        else:
+            p = left + prev - upleft
+            pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - upleft)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, upleft))
+            out = cur - pred
+        raw.append(ft)
+        raw += (out & 255).astype(np.uint8).tobytes()
+        prev = cur
+
+    def chunk(t, d):
+        return struct.pack(">I", len(d)) + t + d + struct.pack(">I", zlib.crc32(t + d) & 0xFFFFFFFF)
+
+    return (b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, ctype, 0, 0, 0))
+            + chunk(b"IDAT", zlib.compress(bytes(raw), level)) + chunk(b"IEND", b""))
+
+
+def write_scene_files(sc: SceneData, directory: str, name: str, anonymous_groups=False) -> None:
+    """Writes `sc` the way the cg24 example scenes are laid out, numbers with repr() (17 significant
+    digits: strtod reads back the very same doubles)."""
+    import os
+    os.makedirs(directory, exist_ok=True)
+    tex_names = []
+    for i, t in enumerate(sc.textures):
+        fn = f"{name}_tex{i}.png"
+        tex_names.append(fn)
+        if t is not None:
+            with open(os.path.join(directory, fn), "wb") as f:
+                f.write(png_bytes(t))
+    with open(os.path.join(directory, name + ".mtl"), "w") as f:
+        for m in sc.materials:
+            f.write(f"newmtl {m.name}\n")
+            f.write("Kd " + " ".join(repr(float(x)) for x in m.kd) + "\n")
+            f.write("Ks " + " ".join(repr(float(x)) for x in m.ks) + "\n")
+            f.write(f"Ns {float(m.ns)!r}\n")
+            if m.kd_tex >= 0:
+                f.write(f"map_Kd {tex_names[m.kd_tex]}\n")
+            f.write("\n")
+    v = np.asarray(sc.vertices, dtype=np.float64).reshape(-1, 3)
+    uv = None if sc.texcoords is None else np.asarray(sc.texcoords, dtype=np.float64).reshape(-1, 2)
+    with open(os.path.join(directory, name + ".obj"), "w") as f:
+        f.write(f"# {sc.name}\nmtllib {name}.mtl\n")
+        for m in range(len(sc.mesh_material)):
+            b, e = int(sc.mesh_first[m]), int(sc.mesh_first[m + 1])
+            f.write("g\n" if anonymous_groups else f"g {sc.mesh_names[m]}\n")
+            f.write(f"usemtl {sc.materials[int(sc.mesh_material[m])].name}\n")
+            for k in range(3 * b, 3 * e):
+                f.write(f"v {float(v[k, 0])!r} {float(v[k, 1])!r} {float(v[k, 2])!r}\n")
+            if uv is not None:
+                for k in range(3 * b, 3 * e):
+                    f.write(f"vt {float(uv[k, 0])!r} {float(uv[k, 1])!r}\n")
+            for t in range(b, e):
+                i = 3 * t + 1
+                # alternate absolute and relative (negative) indices
+                if uv is not None:
+                    if t % 2 == 0:
+                        f.write(f"f {i}/{i} {i + 1}/{i + 1} {i + 2}/{i + 2}\n")
+                    else:
+                        n = 3 * e
+                        f.write(f"f {i - 1 - n}/{i - 1 - n} {i - n}/{i - n} {i + 1 - n}/{i + 1 - n}\n")
+                else:
+                    f.write(f"f {i} {i + 1} {i + 2}\n")
+    cam = sc.camera
+    with open(os.path.join(directory, name + ".xml"), "w") as f:
+        f.write('<?xml version="1.0" encoding="utf-8"?>\n')
+        f.write(f'<camera type="perspective" width="{int(cam["width"])}" height="{int(cam["height"])}" fovy="{float(cam["fovy"])!r}">\n')
+        for tag, key in (("eye", "eye"), ("lookat", "look_at"), ("up", "up")):
+            x, y, z = (float(c) for c in cam[key])
+            f.write(f'    <{tag} x="{x!r}" y="{y!r}" z="{z!r}"/>\n')
+        f.write("</camera>\n<!-- light radiance by material name -->\n")
+        for m in sc.materials:
+            if m.type == capi.MAT_DIFFUSE_LIGHT:
+                f.write(f'<light mtlname="{m.name}" radiance="{float(m.emission[0])!r},{float(m.emission[1])!r},{float(m.emission[2])!r}"/>\n')

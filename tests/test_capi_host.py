@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_every_declared_symbol_is_exported(built):
     hdr = open(os.path.join(ROOT, "include", "prt_b200.h")).read()
-    declared = set(re.findall(r"^(?:int|void|const char\*)\s+(prt_[a-z_0-9]+)\(", hdr, flags=re.M))
+    declared = set(re.findall(r"^(?:int|void|const char\*|const prt_scene_desc\*)\s+(prt_[a-z_0-9]+)\(", hdr, flags=re.M))
     assert len(declared) >= 18
     lib = C.CDLL(capi.LIB_PATH)
     for name in sorted(declared):
