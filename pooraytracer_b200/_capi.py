@@ -25,6 +25,7 @@ MAT_LAMBERTIAN, MAT_PHONG, MAT_MIRROR, MAT_COOK_TORRANCE, MAT_DIFFUSE_LIGHT, MAT
 
 ACCEL_REFERENCE_BVH2 = 0
 ACCEL_SAH_BVH2 = 1
+ACCEL_SAH_BVH4 = 2
 
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2

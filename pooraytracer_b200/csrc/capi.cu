@@ -88,6 +88,7 @@ struct prt_scene {
     DevBuf<int32_t> d_slot_prim;
     DevBuf<TriShade> d_shade;
     DevBuf<Node2> d_nodes2;
+    DevBuf<Node4> d_nodes4;
     DevBuf<RefNode> d_ref_nodes;
     DevBuf<LightTri> d_light_tris;
     DevBuf<LightNode> d_light_nodes;
@@ -290,20 +291,21 @@ void prt_scene_destroy(prt_scene* scene) {
 int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_scene_commit: null scene");
     const int accel = opts ? opts->accel : PRT_ACCEL_SAH_BVH2;
-    if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2) return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
+    if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2 && accel != PRT_ACCEL_SAH_BVH4) return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
     HostScene& h = s->host;
     try {
         int max_leaf = opts && opts->reserved[0] > 0 ? opts->reserved[0] : 4;
         if (accel == PRT_ACCEL_SAH_BVH2) h.build_sah_bvh2(default_host_threads(), max_leaf);
+        else if (accel == PRT_ACCEL_SAH_BVH4) h.build_sah_bvh4(default_host_threads(), max_leaf);
         else h.use_reference_slots();
         h.flatten_reference_world();
     } catch (const std::bad_alloc&) {
         return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_commit: out of host memory");
     }
     s->accel = accel;
-    s->stats.node_bytes = accel == PRT_ACCEL_SAH_BVH2 ? PRT_NODE2_BYTES : PRT_REFNODE_BYTES;
+    s->stats.node_bytes = accel == PRT_ACCEL_SAH_BVH2 ? PRT_NODE2_BYTES : (accel == PRT_ACCEL_SAH_BVH4 ? PRT_NODE4_BYTES : PRT_REFNODE_BYTES);
     s->stats.tri_bytes = PRT_TRI_BYTES;
-    s->stats.n_nodes = accel == PRT_ACCEL_SAH_BVH2 ? (int64_t)h.nodes2.size() : (int64_t)h.ref_flat.size();
+    s->stats.n_nodes = accel == PRT_ACCEL_SAH_BVH2 ? (int64_t)h.nodes2.size() : (accel == PRT_ACCEL_SAH_BVH4 ? (int64_t)h.nodes4.size() : (int64_t)h.ref_flat.size());
     s->stats.n_triangles = h.n_tris;
     if (s->ctx->device < 0) { /* host-only context: flattening done, nothing to upload */
         s->committed = true;
@@ -331,6 +333,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     CUDA_TRY(s->d_slot_prim.upload(h.slot_prim, st));
     CUDA_TRY(s->d_shade.upload(h.shade, st));
     CUDA_TRY(s->d_nodes2.upload(h.nodes2, st));
+    CUDA_TRY(s->d_nodes4.upload(h.nodes4, st));
     CUDA_TRY(s->d_ref_nodes.upload(h.ref_flat, st));
     CUDA_TRY(s->d_light_tris.upload(h.light_tris, st));
     CUDA_TRY(s->d_light_nodes.upload(h.light_nodes, st));
@@ -348,6 +351,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     D.slot_prim = s->d_slot_prim.p;
     D.shade = s->d_shade.p;
     D.nodes2 = accel == PRT_ACCEL_SAH_BVH2 && !h.nodes2.empty() ? s->d_nodes2.p : nullptr;
+    D.nodes4 = accel == PRT_ACCEL_SAH_BVH4 && !h.nodes4.empty() ? s->d_nodes4.p : nullptr;
     D.ref_nodes = s->d_ref_nodes.p;
     D.ref_root = h.ref_root_flat;
     D.n_nodes2 = (int32_t)h.nodes2.size();

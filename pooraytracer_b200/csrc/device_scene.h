@@ -60,6 +60,18 @@ struct alignas(64) Node2 {
     int32_t pad[2];
 };
 
+/* SAH BVH4: the BVH2 collapsed (grandchildren pulled up by largest surface area), four child boxes
+ * per node as outward-rounded FP32, stored per axis across the children so that one 128-bit load
+ * brings the same bound of all four. 128 bytes = one L2 line = seven 128-bit loads (112 B used).
+ * Child references as in Node2; an unused slot holds PRT_NO_CHILD. */
+#define PRT_NODE4_BYTES 128
+struct alignas(128) Node4 {
+    float lo[3][4]; /* lo[axis][child] */
+    float hi[3][4];
+    int32_t child[4];
+    int32_t pad[4];
+};
+
 /* The reference's own median-split BVH, flattened (Source/BVH.cpp:7-48): FP64 box, children in the
  * reference's left/right order. ref >= 0: node; ref < 0: ~slot of a triangle. */
 #define PRT_REFNODE_BYTES 64
@@ -93,6 +105,7 @@ struct DevScene {
     const int32_t* slot_prim;  /* [n_tris] slot -> prim id */
     const TriShade* shade;     /* [n_tris] prim order */
     const Node2* nodes2;       /* SAH BVH2 (root = 0) or nullptr */
+    const Node4* nodes4;       /* SAH BVH4 (root = 0) or nullptr */
     const RefNode* ref_nodes;  /* reference BVH */
     int32_t ref_root;          /* -1: empty world */
     int32_t n_nodes2;

@@ -128,24 +128,24 @@ struct AnyQueryPolicy {
     __device__ __forceinline__ void finish() const {}
 };
 
-template <bool COUNT>
+template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                        const double* __restrict__ tmin, const double* __restrict__ tmax,
                                                        int32_t* __restrict__ prim, double* __restrict__ t, double* __restrict__ alpha,
                                                        double* __restrict__ beta, int32_t* fetch, unsigned long long* counters) {
     VisitCounters cnt = {0, 0};
     ClosestQueryPolicy pol = {o, d, tmin, tmax, prim, t, alpha, beta, S.slot_prim};
-    traverse_persistent<false, COUNT>(S, pol, fetch, (int32_t)n, cnt);
+    traverse_persistent<false, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
 }
 
-template <bool COUNT>
+template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                    const double* __restrict__ tmin, const double* __restrict__ tmax, uint8_t* __restrict__ hit,
                                                    int32_t* fetch, unsigned long long* counters) {
     VisitCounters cnt = {0, 0};
     AnyQueryPolicy pol = {o, d, tmin, tmax, hit};
-    traverse_persistent<true, COUNT>(S, pol, fetch, (int32_t)n, cnt);
+    traverse_persistent<true, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
 }
 
@@ -295,13 +295,13 @@ struct ExtendPolicy {
     __device__ __forceinline__ void finish() { flush(); }
 };
 
-template <bool COUNT>
+template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = bounce == 0 ? rc.n_paths : ctrl->n_extend;
     VisitCounters cnt = {0, 0};
     ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, pb.q_extend[bounce & 1], bounce, {-1, 0, 0}};
-    traverse_persistent<false, COUNT>(S, pol, &ctrl->fetch_extend, n, cnt);
+    traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_extend, n, cnt);
     flush_counters<COUNT>(cnt, pb.counters);
 }
 
@@ -482,17 +482,17 @@ struct ShadowPolicy {
     }
 };
 
-template <bool COUNT>
+template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = ctrl->n_shadow;
     VisitCounters cnt = {0, 0};
     if (rc.flags & PRT_RENDER_EXACT_VISIBILITY) {
         ShadowPolicy<true> pol = {pb, pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
-        traverse_persistent<false, COUNT>(S, pol, &ctrl->fetch_shadow, n, cnt);
+        traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
     } else {
         ShadowPolicy<false> pol = {pb, pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
-        traverse_persistent<true, COUNT>(S, pol, &ctrl->fetch_shadow, n, cnt);
+        traverse_persistent<true, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
     }
     flush_counters<COUNT>(cnt, pb.counters);
 }
@@ -572,18 +572,33 @@ static int persistent_grid(K kernel, int block, const LaunchConfig& lc, int64_t 
     return (int)(want < cap ? want : cap);
 }
 
+/* picks the <COUNT, WIDE> instantiation of a traversal kernel; GRID may name it as KERNEL */
+#define PRT_DISPATCH_ONE(C, W, NAME, GRID, ARGS)      \
+    do {                                              \
+        auto KERNEL = NAME<C, W>;                     \
+        KERNEL<<<(GRID), 128, 0, st>>> ARGS;          \
+    } while (0)
+#define PRT_DISPATCH(count, wide, NAME, GRID, ARGS)                            \
+    do {                                                                       \
+        if (count) {                                                           \
+            if (wide) PRT_DISPATCH_ONE(true, 4, NAME, GRID, ARGS);             \
+            else PRT_DISPATCH_ONE(true, 2, NAME, GRID, ARGS);                  \
+        } else {                                                               \
+            if (wide) PRT_DISPATCH_ONE(false, 4, NAME, GRID, ARGS);            \
+            else PRT_DISPATCH_ONE(false, 2, NAME, GRID, ARGS);                 \
+        }                                                                      \
+    } while (0)
+
 void launch_trace_closest(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
                           int32_t* prim, double* t, double* alpha, double* beta, int32_t* fetch, unsigned long long* counters,
                           const LaunchConfig& lc, cudaStream_t st) {
     if (n <= 0) return;
-    if (counters) k_trace_closest<true><<<persistent_grid(k_trace_closest<true>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters);
-    else k_trace_closest<false><<<persistent_grid(k_trace_closest<false>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters);
+    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_closest, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters));
 }
 void launch_trace_any(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
                       uint8_t* hit, int32_t* fetch, unsigned long long* counters, const LaunchConfig& lc, cudaStream_t st) {
     if (n <= 0) return;
-    if (counters) k_trace_any<true><<<persistent_grid(k_trace_any<true>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, hit, fetch, counters);
-    else k_trace_any<false><<<persistent_grid(k_trace_any<false>, 128, lc, n), 128, 0, st>>>(S, n, o, d, tmin, tmax, hit, fetch, counters);
+    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_any, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, hit, fetch, counters));
 }
 void launch_sample_lights(const DevScene& S, int64_t n, const double* origins, const double* u, double* position, double* normal,
                           uint8_t* front, double* pdf, int32_t* prim, cudaStream_t st) {
@@ -597,8 +612,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int n_bounces = rc.max_depth + 1;
     cudaMemsetAsync(pb.ctrl, 0, sizeof(BounceCtrl) * (size_t)(n_bounces + 1), st);
     const bool count = (rc.flags & PRT_RENDER_COUNTERS) != 0;
-    const int g_extend = count ? persistent_grid(k_extend<true>, 128, lc, rc.n_paths) : persistent_grid(k_extend<false>, 128, lc, rc.n_paths);
-    const int g_shadow = count ? persistent_grid(k_shadow<true>, 128, lc, rc.n_paths) : persistent_grid(k_shadow<false>, 128, lc, rc.n_paths);
+    const bool wide = S.nodes4 != nullptr;
     LaunchConfig shade_lc = lc;
     shade_lc.trace_blocks_per_sm = 0;
     const int g_shade0 = persistent_grid(k_shade<CLS_LAMBERT>, 128, shade_lc, rc.n_paths);
@@ -608,8 +622,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     cudaEvent_t* ev = lc.stage_events;
     for (int b = 0; b < n_bounces; ++b) {
         if (ev) cudaEventRecord(ev[4 * b], st);
-        if (count) k_extend<true><<<g_extend, 128, 0, st>>>(S, prim_class, rc, pb, b);
-        else k_extend<false><<<g_extend, 128, 0, st>>>(S, prim_class, rc, pb, b);
+        PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, prim_class, rc, pb, b));
         if (ev) cudaEventRecord(ev[4 * b + 1], st);
         k_shade<CLS_LAMBERT><<<g_shade0, 128, 0, st>>>(S, rc, pb, b);
         k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b);
@@ -621,8 +634,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         }
         if (ev) cudaEventRecord(ev[4 * b + 2], st);
         if (rc.sample_lights) {
-            if (count) k_shadow<true><<<g_shadow, 128, 0, st>>>(S, rc, pb, b);
-            else k_shadow<false><<<g_shadow, 128, 0, st>>>(S, rc, pb, b);
+            PRT_DISPATCH(count, wide, k_shadow, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, rc, pb, b));
             ++launches;
         }
         if (ev) cudaEventRecord(ev[4 * b + 3], st);

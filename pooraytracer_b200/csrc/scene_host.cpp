@@ -550,22 +550,36 @@ inline void set_child_box(float* lo, float* hi, const Box6& b) {
 
 }  // namespace
 
+/* binned-SAH binary tree over all triangles (TmpNode[0] = root) + the permuted index array */
+static void build_sah_tree(HostScene& s, int n_threads, int max_leaf, std::vector<int32_t>& idx, std::vector<TmpNode>& tmp) {
+    idx.resize((size_t)s.n_tris);
+    for (int64_t i = 0; i < s.n_tris; ++i) idx[i] = (int32_t)i;
+    tmp.assign((size_t)(2 * s.n_tris + 1), TmpNode());
+    std::atomic<int32_t> next{1};
+    int par = 0;
+    while ((1 << par) < n_threads) ++par;
+    SahBuilder b{s, idx, tmp, next, max_leaf};
+    b.build(0, 0, (int32_t)s.n_tris, par + 1);
+}
+
+static void finish_slots(HostScene& s) {
+    for (size_t sidx = 0; sidx < s.slot_prim.size(); ++sidx) s.prim_slot[s.slot_prim[sidx]] = (int32_t)sidx;
+    s.isect_slots.resize((size_t)s.n_tris);
+    for (int64_t sidx = 0; sidx < s.n_tris; ++sidx) s.isect_slots[sidx] = s.isect[s.slot_prim[sidx]];
+}
+
 void HostScene::build_sah_bvh2(int n_threads, int max_leaf) {
     nodes2.clear();
+    nodes4.clear();
     slot_prim.clear();
     prim_slot.assign((size_t)n_tris, -1);
     if (max_leaf < 1) max_leaf = 1;
     if (max_leaf > 8) max_leaf = 8;
     sah_max_leaf = max_leaf;
     if (n_tris == 0) return;
-    std::vector<int32_t> idx((size_t)n_tris);
-    for (int64_t i = 0; i < n_tris; ++i) idx[i] = (int32_t)i;
-    std::vector<TmpNode> tmp((size_t)(2 * n_tris + 1));
-    std::atomic<int32_t> next{1};
-    int par = 0;
-    while ((1 << par) < n_threads) ++par;
-    SahBuilder b{*this, idx, tmp, next, max_leaf};
-    b.build(0, 0, (int32_t)n_tris, par + 1);
+    std::vector<int32_t> idx;
+    std::vector<TmpNode> tmp;
+    build_sah_tree(*this, n_threads, max_leaf, idx, tmp);
 
     /* flatten in DFS preorder; leaves define the slot order */
     slot_prim.reserve((size_t)n_tris);
@@ -611,13 +625,94 @@ void HostScene::build_sah_bvh2(int n_threads, int max_leaf) {
             if (L.left >= 0) stack.push_back({n.left, c0});
         }
     }
-    for (size_t sidx = 0; sidx < slot_prim.size(); ++sidx) prim_slot[slot_prim[sidx]] = (int32_t)sidx;
-    isect_slots.resize((size_t)n_tris);
-    for (int64_t sidx = 0; sidx < n_tris; ++sidx) isect_slots[sidx] = isect[slot_prim[sidx]];
+    finish_slots(*this);
+}
+
+/* BVH4 = the binned-SAH binary tree with, at every node, the inner child of largest surface area
+ * replaced by its own two children until four children are held (or only leaves remain). The boxes
+ * are the binary tree's, so everything said about Node2 (outward FP32 rounding, containment of the
+ * reference's boxes) holds unchanged. */
+void HostScene::build_sah_bvh4(int n_threads, int max_leaf) {
+    nodes2.clear();
+    nodes4.clear();
+    slot_prim.clear();
+    prim_slot.assign((size_t)n_tris, -1);
+    if (max_leaf < 1) max_leaf = 1;
+    if (max_leaf > 8) max_leaf = 8;
+    sah_max_leaf = max_leaf;
+    if (n_tris == 0) return;
+    std::vector<int32_t> idx;
+    std::vector<TmpNode> tmp;
+    build_sah_tree(*this, n_threads, max_leaf, idx, tmp);
+
+    slot_prim.reserve((size_t)n_tris);
+    auto leaf_ref = [&](const TmpNode& n) -> int32_t {
+        const int32_t first_slot = (int32_t)slot_prim.size();
+        for (int32_t i = n.first; i < n.first + n.count; ++i) slot_prim.push_back(idx[i]);
+        return ~((first_slot << 3) | (n.count - 1));
+    };
+    auto area_of = [](const Box6& b) {
+        const double dx = b.v[1] - b.v[0], dy = b.v[3] - b.v[2], dz = b.v[5] - b.v[4];
+        return dx * dy + dy * dz + dz * dx;
+    };
+    const int32_t NO_CHILD = INT32_MIN;
+    const float inf = std::numeric_limits<float>::infinity();
+    struct Work { int32_t tmp_idx, flat_idx; };
+    std::vector<Work> stack;
+    nodes4.emplace_back();
+    stack.push_back({0, 0});
+    while (!stack.empty()) {
+        Work w = stack.back();
+        stack.pop_back();
+        int32_t kids[4];
+        int nk = 0;
+        if (tmp[w.tmp_idx].left < 0) {
+            kids[nk++] = w.tmp_idx; /* the whole scene is one leaf */
+        } else {
+            kids[nk++] = tmp[w.tmp_idx].left;
+            kids[nk++] = tmp[w.tmp_idx].right;
+            while (nk < 4) {
+                int best = -1;
+                double best_area = -1.0;
+                for (int i = 0; i < nk; ++i)
+                    if (tmp[kids[i]].left >= 0) {
+                        const double a = area_of(tmp[kids[i]].box);
+                        if (a > best_area) { best_area = a; best = i; }
+                    }
+                if (best < 0) break;
+                const int32_t t = kids[best];
+                for (int i = nk; i > best + 1; --i) kids[i] = kids[i - 1]; /* keep the left-to-right order */
+                kids[best] = tmp[t].left;
+                kids[best + 1] = tmp[t].right;
+                ++nk;
+            }
+        }
+        Node4 out;
+        std::memset(&out, 0, sizeof(out));
+        int32_t refs[4];
+        for (int i = 0; i < 4; ++i) {
+            if (i < nk) {
+                float lo[3], hi[3];
+                set_child_box(lo, hi, tmp[kids[i]].box);
+                for (int k = 0; k < 3; ++k) { out.lo[k][i] = lo[k]; out.hi[k][i] = hi[k]; }
+                if (tmp[kids[i]].left < 0) refs[i] = leaf_ref(tmp[kids[i]]);
+                else { refs[i] = (int32_t)nodes4.size(); nodes4.emplace_back(); }
+            } else {
+                for (int k = 0; k < 3; ++k) { out.lo[k][i] = inf; out.hi[k][i] = -inf; }
+                refs[i] = NO_CHILD;
+            }
+            out.child[i] = refs[i];
+        }
+        nodes4[w.flat_idx] = out;
+        for (int i = nk - 1; i >= 0; --i)
+            if (refs[i] >= 0) stack.push_back({kids[i], refs[i]});
+    }
+    finish_slots(*this);
 }
 
 void HostScene::use_reference_slots() {
     nodes2.clear();
+    nodes4.clear();
     slot_prim.assign((size_t)n_tris, 0);
     prim_slot.assign((size_t)n_tris, -1);
     for (int64_t p = 0; p < n_tris; ++p) {

@@ -38,10 +38,46 @@ struct VisitCounters {
 #define PRT_COUNT_NODE(c) do { if (COUNT) (c).nodes++; } while (0)
 #define PRT_COUNT_TRI(c) do { if (COUNT) (c).tris++; } while (0)
 
-/* Triangle::Hit. The 128-byte record is read as 2 + 6 128-bit loads: the plane first, the rest
+/* 256-bit read-only loads (sm_100: LDG.E.256): one L1 request per 32 bytes of a lane's record. The
+ * traversal kernels are bound by L1TEX request throughput (ncu: l1tex__throughput 70-80 % of peak
+ * with the issue slots half idle), every lane fetching its own node / triangle line, so halving
+ * the number of load instructions per record is what counts. */
+#ifndef PRT_LD256
+#define PRT_LD256 1
+#endif
+struct f8 { float v[8]; };
+struct dd4 { double v[4]; };
+__device__ __forceinline__ f8 ld256f(const void* p) {
+    f8 r;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+        : "l"(p));
+    return r;
+}
+__device__ __forceinline__ dd4 ld256d(const void* p) {
+    dd4 r;
+    asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.v[0]), "=d"(r.v[1]), "=d"(r.v[2]), "=d"(r.v[3]) : "l"(p));
+    return r;
+}
+
+/* Triangle::Hit. The 128-byte record is read as the plane (32 B) first and the remaining 96 B
  * only for candidates whose t is inside the interval. */
 __device__ __forceinline__ bool tri_test(const TriIsect* __restrict__ T, d3 o, d3 d, double tmin, double tmax,
                                          double& t_out, double& alpha_out, double& beta_out) {
+#if PRT_LD256
+    const char* __restrict__ p = reinterpret_cast<const char*>(T);
+    const dd4 q0 = ld256d(p); /* n.x n.y n.z D */
+    const d3 n = mk3(q0.v[0], q0.v[1], q0.v[2]);
+    const double denom = dot(n, d);
+    if (fabs(denom) < 1e-8) return false;
+    const double t = (q0.v[3] - dot(n, o)) / denom;
+    if (!(tmin <= t && t <= tmax)) return false; /* Interval::Contains, inclusive */
+    const dd4 q1 = ld256d(p + 32), q2 = ld256d(p + 64), q3 = ld256d(p + 96);
+    const d3 w = mk3(q1.v[0], q1.v[1], q1.v[2]);
+    const d3 v0 = mk3(q1.v[3], q2.v[0], q2.v[1]);
+    const d3 e0 = mk3(q2.v[2], q2.v[3], q3.v[0]);
+    const d3 e1 = mk3(q3.v[1], q3.v[2], q3.v[3]);
+#else
     const double2* __restrict__ p = reinterpret_cast<const double2*>(T);
     const double2 q0 = __ldg(p), q1 = __ldg(p + 1); /* n.x n.y | n.z D */
     const d3 n = mk3(q0.x, q0.y, q1.x);
@@ -54,6 +90,7 @@ __device__ __forceinline__ bool tri_test(const TriIsect* __restrict__ T, d3 o, d
     const d3 v0 = mk3(q3.y, q4.x, q4.y);
     const d3 e0 = mk3(q5.x, q5.y, q6.x);
     const d3 e1 = mk3(q6.y, q7.x, q7.y);
+#endif
     const d3 pt = o + d * t; /* Ray.h:13 */
     const d3 v0p = pt - v0;
     const double alpha = dot(w, cross(v0p, e1));

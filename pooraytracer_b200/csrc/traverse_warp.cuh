@@ -126,7 +126,7 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
  * Results are the reference's (see traverse.cuh): boundary and equal-t hits go through
  * trace_reference before they are retired.
  */
-template <bool ANY, bool COUNT, class P>
+template <bool ANY, bool COUNT, int WIDE, class P>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, int32_t* cursor, int32_t n, VisitCounters& cnt) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -143,7 +143,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     RayF32 rf = make_ray_f32(o, d);
     Hit hit;
     hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
-    const bool use_sah = S.nodes2 != nullptr;
+    const bool use_sah = WIDE == 4 ? S.nodes4 != nullptr : S.nodes2 != nullptr;
 
     /* fetch pipeline state (c_*, b_base, b_pref are warp-uniform) */
     int32_t a_raw = 0;                 /* lane 0: chunk A's atomic result */
@@ -295,23 +295,72 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
              * the leaf phase and carry on in the next round */
             for (;;) {
                 if (cur >= 0 && cur != PRT_DONE) {
-                    const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes2 + cur);
-                    const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-                    const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
                     if (COUNT) cnt.nodes++;
-                    float e0, e1;
-                    const bool h0 = box_f32(a.x, a.y, a.z, a.w, b.x, b.y, rf, tmin32, tbest32, e0);
-                    const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
-                    if (h0 && h1) {
-                        const bool swap = e1 < e0;
-                        if (sp < PRT_STACK) stack[sp++] = swap ? ch.x : ch.y;
-                        cur = swap ? ch.y : ch.x;
-                    } else if (h0) {
-                        cur = ch.x;
-                    } else if (h1) {
-                        cur = ch.y;
+                    if (WIDE == 4) {
+#if PRT_LD256
+                        const char* __restrict__ p = reinterpret_cast<const char*>(S.nodes4 + cur);
+                        const f8 q0 = ld256f(p), q1 = ld256f(p + 32), q2 = ld256f(p + 64), q3 = ld256f(p + 96);
+                        const float4 lx = make_float4(q0.v[0], q0.v[1], q0.v[2], q0.v[3]), ly = make_float4(q0.v[4], q0.v[5], q0.v[6], q0.v[7]);
+                        const float4 lz = make_float4(q1.v[0], q1.v[1], q1.v[2], q1.v[3]), hx = make_float4(q1.v[4], q1.v[5], q1.v[6], q1.v[7]);
+                        const float4 hy = make_float4(q2.v[0], q2.v[1], q2.v[2], q2.v[3]), hz = make_float4(q2.v[4], q2.v[5], q2.v[6], q2.v[7]);
+                        const int4 ch = make_int4(__float_as_int(q3.v[0]), __float_as_int(q3.v[1]), __float_as_int(q3.v[2]), __float_as_int(q3.v[3]));
+#else
+                        const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes4 + cur);
+                        const float4 lx = __ldg(p), ly = __ldg(p + 1), lz = __ldg(p + 2);
+                        const float4 hx = __ldg(p + 3), hy = __ldg(p + 4), hz = __ldg(p + 5);
+                        const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 6));
+#endif
+                        float e0, e1, e2, e3;
+                        const bool h0 = box_f32(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, rf, tmin32, tbest32, e0);
+                        const bool h1 = box_f32(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
+                        const bool h2 = box_f32(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, rf, tmin32, tbest32, e2) && ch.z != PRT_NO_CHILD;
+                        const bool h3 = box_f32(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, rf, tmin32, tbest32, e3) && ch.w != PRT_NO_CHILD;
+                        /* sort the hit children by entry distance: key = distance bits (non-negative
+                         * float: ordered like an unsigned) with the child's slot in the two low bits */
+                        const unsigned MISS = 0xffffffffu;
+                        const unsigned k0 = h0 ? ((__float_as_uint(fmaxf(e0, 0.f)) & ~3u) | 0u) : MISS;
+                        const unsigned k1 = h1 ? ((__float_as_uint(fmaxf(e1, 0.f)) & ~3u) | 1u) : MISS;
+                        const unsigned k2 = h2 ? ((__float_as_uint(fmaxf(e2, 0.f)) & ~3u) | 2u) : MISS;
+                        const unsigned k3 = h3 ? ((__float_as_uint(fmaxf(e3, 0.f)) & ~3u) | 3u) : MISS;
+                        const unsigned a0 = min(k0, k1), a1 = max(k0, k1), b0 = min(k2, k3), b1 = max(k2, k3);
+                        const unsigned s0 = min(a0, b0), t1 = max(a0, b0), t2 = min(a1, b1), s3 = max(a1, b1);
+                        const unsigned s1 = min(t1, t2), s2 = max(t1, t2);
+#define PRT_CHILD_OF(key) (((key) & 2u) ? (((key) & 1u) ? ch.w : ch.z) : (((key) & 1u) ? ch.y : ch.x))
+                        if (s0 == MISS) {
+                            cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                        } else {
+                            if (s3 != MISS && sp < PRT_STACK) stack[sp++] = PRT_CHILD_OF(s3);
+                            if (s2 != MISS && sp < PRT_STACK) stack[sp++] = PRT_CHILD_OF(s2);
+                            if (s1 != MISS && sp < PRT_STACK) stack[sp++] = PRT_CHILD_OF(s1);
+                            cur = PRT_CHILD_OF(s0);
+                        }
+#undef PRT_CHILD_OF
                     } else {
-                        cur = sp > 0 ? stack[--sp] : PRT_DONE;
+#if PRT_LD256
+                        const char* __restrict__ p = reinterpret_cast<const char*>(S.nodes2 + cur);
+                        const f8 q0 = ld256f(p), q1 = ld256f(p + 32);
+                        const float4 a = make_float4(q0.v[0], q0.v[1], q0.v[2], q0.v[3]), b = make_float4(q0.v[4], q0.v[5], q0.v[6], q0.v[7]);
+                        const float4 c = make_float4(q1.v[0], q1.v[1], q1.v[2], q1.v[3]);
+                        const int4 ch = make_int4(__float_as_int(q1.v[4]), __float_as_int(q1.v[5]), 0, 0);
+#else
+                        const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes2 + cur);
+                        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+                        const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
+#endif
+                        float e0, e1;
+                        const bool h0 = box_f32(a.x, a.y, a.z, a.w, b.x, b.y, rf, tmin32, tbest32, e0);
+                        const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
+                        if (h0 && h1) {
+                            const bool swap = e1 < e0;
+                            if (sp < PRT_STACK) stack[sp++] = swap ? ch.x : ch.y;
+                            cur = swap ? ch.y : ch.x;
+                        } else if (h0) {
+                            cur = ch.x;
+                        } else if (h1) {
+                            cur = ch.y;
+                        } else {
+                            cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                        }
                     }
                 }
                 if (__popc(__ballot_sync(FULL, cur >= 0 && cur != PRT_DONE)) < PRT_INNER_EXIT_BELOW) break;

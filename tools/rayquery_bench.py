@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--check", type=int, default=0, help="compare the first N rays with the CPU oracle")
     ap.add_argument("--max-leaf", type=int, default=0)
+    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh2"), choices=["bvh2", "bvh4"])
     a = ap.parse_args()
     import torch
     from pooraytracer_b200 import Context, Scene, _capi as capi, scenes
@@ -41,7 +42,7 @@ def main():
     t0 = time.time()
     import ctypes as C
     o_ = capi.PrtBuildOpts()
-    o_.accel = capi.ACCEL_SAH_BVH2
+    o_.accel = capi.ACCEL_SAH_BVH4 if a.accel == "bvh4" else capi.ACCEL_SAH_BVH2
     o_.reserved[0] = a.max_leaf
     rc = scene.lib.prt_scene_commit(scene.handle, C.byref(o_))
     assert rc == 0, scene.lib.prt_last_error()
