@@ -57,7 +57,7 @@ def parse():
     ap.add_argument("--depth", type=int, default=DEPTH)
     ap.add_argument("--scene", default="cornell-box", choices=["cornell-box", "veach-mis", "bathroom2"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh2"), choices=["bvh2", "bvh4"])
+    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4"])
     ap.add_argument("--cpu-spp", type=int, default=1, help="spp of the bounded CPU sample")
     return ap.parse_args()
 

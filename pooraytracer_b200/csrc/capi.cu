@@ -114,6 +114,10 @@ struct prt_scene {
     DevBuf<PathRec> p_rec;
     DevBuf<int32_t> p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qm3, p_qs;
     DevBuf<BounceCtrl> p_ctrl;
+    /* ray binning (launch.h): keys, reordered queues, histograms + cursors; also used by the ray queries */
+    DevBuf<uint16_t> p_ke, p_ks;
+    DevBuf<int32_t> p_qse, p_qss, p_hist, p_cursor;
+    float key_lo[3] = {0.f, 0.f, 0.f}, key_scale[3] = {0.f, 0.f, 0.f};
     int64_t pool_cap = 0;
     int pool_bounces = 0;
 
@@ -148,7 +152,20 @@ LaunchConfig launch_config(const prt_context* ctx) {
     const char* env = std::getenv("PRT_BLOCKS_PER_SM");
     lc.trace_blocks_per_sm = env ? std::max(1, std::atoi(env)) : 0; /* 0 = whatever is resident */
     lc.stage_events = nullptr;
+    /* PRT_SORT_MIN: shortest (expected) ray queue that is binned before it is traced; 0 = never, the
+     * default: measured on B200 (profiles/r1_s4_binning_ab.txt) the 16^3 x 8-octant bins buy 2-6 % of
+     * traversal time and cost more than that in histogram atomics and the scatter pass */
+    env = std::getenv("PRT_SORT_MIN");
+    lc.sort_min = env ? std::max<int64_t>(0, std::atoll(env)) : 0;
     return lc;
+}
+
+int ensure_sort_scratch(prt_scene* s, cudaStream_t st) {
+    if (s->p_hist.p) return PRT_OK;
+    CUDA_TRY(s->p_hist.ensure((size_t)2 * PRT_KEY_BINS));
+    CUDA_TRY(s->p_cursor.ensure((size_t)2 * PRT_KEY_BINS));
+    CUDA_TRY(cudaMemsetAsync(s->p_hist.p, 0, sizeof(int32_t) * 2 * PRT_KEY_BINS, st)); /* k_sort_scan keeps it zero */
+    return PRT_OK;
 }
 
 int64_t pass_path_budget() {
@@ -168,6 +185,10 @@ int ensure_pool(prt_scene* s, int64_t cap, int n_bounces) {
         CUDA_TRY(s->p_qm2.ensure((size_t)cap));
         CUDA_TRY(s->p_qm3.ensure((size_t)cap));
         CUDA_TRY(s->p_qs.ensure((size_t)cap));
+        CUDA_TRY(s->p_ke.ensure((size_t)cap));
+        CUDA_TRY(s->p_ks.ensure((size_t)cap));
+        CUDA_TRY(s->p_qse.ensure((size_t)cap));
+        CUDA_TRY(s->p_qss.ensure((size_t)cap));
         s->pool_cap = cap;
     }
     if (n_bounces + 2 > s->pool_bounces) {
@@ -185,6 +206,9 @@ PathBuffers path_buffers(prt_scene* s) {
     pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p; pb.q_mat[3] = s->p_qm3.p;
     pb.q_shadow = s->p_qs.p;
     pb.ctrl = s->p_ctrl.p;
+    pb.key_extend = s->p_ke.p; pb.key_shadow = s->p_ks.p;
+    pb.qs_extend = s->p_qse.p; pb.qs_shadow = s->p_qss.p;
+    pb.hist = s->p_hist.p; pb.cursor = s->p_cursor.p;
     pb.counters = s->count_visits ? s->d_counters.p : nullptr;
     return pb;
 }
@@ -307,6 +331,20 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     s->stats.tri_bytes = PRT_TRI_BYTES;
     s->stats.n_nodes = accel == PRT_ACCEL_SAH_BVH2 ? (int64_t)h.nodes2.size() : (accel == PRT_ACCEL_SAH_BVH4 ? (int64_t)h.nodes4.size() : (int64_t)h.ref_flat.size());
     s->stats.n_triangles = h.n_tris;
+    { /* ray-binning grid: PRT_KEY_GRID^3 cells over the bounding box of all triangles */
+        double lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+        for (int64_t p = 0; p < h.n_tris; ++p)
+            for (int k = 0; k < 3; ++k) {
+                const double a = h.tri_box[p].v[2 * k], b = h.tri_box[p].v[2 * k + 1];
+                if (p == 0 || a < lo[k]) lo[k] = a;
+                if (p == 0 || b > hi[k]) hi[k] = b;
+            }
+        for (int k = 0; k < 3; ++k) {
+            const double ext = hi[k] - lo[k];
+            s->key_lo[k] = (float)lo[k];
+            s->key_scale[k] = ext > 0.0 && std::isfinite(ext) ? (float)(PRT_KEY_GRID / ext) : 0.f;
+        }
+    }
     if (s->ctx->device < 0) { /* host-only context: flattening done, nothing to upload */
         s->committed = true;
         return PRT_OK;
@@ -345,6 +383,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     CUDA_TRY(s->d_fetch.ensure(4));
     CUDA_TRY(s->d_counters.ensure(4));
     CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
+    if (int e = ensure_sort_scratch(s, st)) return e;
     CUDA_TRY(cudaStreamSynchronize(st));
     DevScene& D = s->dev;
     D.tris = s->d_tris.p;
@@ -397,6 +436,18 @@ static int trace_begin(prt_scene* s, int64_t n, cudaStream_t st) {
     CUDA_TRY(cudaEventRecord(s->ev0, st));
     return PRT_OK;
 }
+/* ray binning of a query batch (inside the timed region): *order = the binned ray order, or nullptr
+ * for a batch too short to be worth three more launches */
+static int query_order(prt_scene* s, int64_t n, const double* o, const double* d, const LaunchConfig& lc, cudaStream_t st,
+                       const int32_t** order) {
+    *order = nullptr;
+    if (lc.sort_min <= 0 || n < lc.sort_min) return PRT_OK;
+    CUDA_TRY(s->p_ke.ensure((size_t)n));
+    CUDA_TRY(s->p_qse.ensure((size_t)n));
+    launch_query_sort(n, o, d, s->key_lo, s->key_scale, s->p_ke.p, s->p_hist.p, s->p_cursor.p, s->p_qse.p, lc, st);
+    *order = s->p_qse.p;
+    return PRT_OK;
+}
 static int trace_end(prt_scene* s, int64_t n, bool shadow, cudaStream_t st) {
     CUDA_TRY(cudaEventRecord(s->ev1, st));
     CUDA_TRY(cudaGetLastError());
@@ -419,8 +470,12 @@ int prt_trace_closest_device(prt_scene* s, int64_t n, const double* o, const dou
     cudaStream_t st = stream ? (cudaStream_t)stream : s->ctx->stream;
     rc = trace_begin(s, n, st);
     if (rc) return rc;
-    launch_trace_closest(s->dev, n, o, d, tmin, tmax, prim, t, alpha, beta, s->d_fetch.p, s->count_visits ? s->d_counters.p : nullptr,
-                         launch_config(s->ctx), st);
+    const LaunchConfig lc = launch_config(s->ctx);
+    const int32_t* order = nullptr;
+    rc = query_order(s, n, o, d, lc, st, &order);
+    if (rc) return rc;
+    launch_trace_closest(s->dev, n, o, d, tmin, tmax, prim, t, alpha, beta, order, s->d_fetch.p, s->count_visits ? s->d_counters.p : nullptr,
+                         lc, st);
     return trace_end(s, n, false, st);
 }
 
@@ -432,7 +487,11 @@ int prt_trace_any_device(prt_scene* s, int64_t n, const double* o, const double*
     cudaStream_t st = stream ? (cudaStream_t)stream : s->ctx->stream;
     rc = trace_begin(s, n, st);
     if (rc) return rc;
-    launch_trace_any(s->dev, n, o, d, tmin, tmax, hit, s->d_fetch.p, s->count_visits ? s->d_counters.p : nullptr, launch_config(s->ctx), st);
+    const LaunchConfig lc = launch_config(s->ctx);
+    const int32_t* order = nullptr;
+    rc = query_order(s, n, o, d, lc, st, &order);
+    if (rc) return rc;
+    launch_trace_any(s->dev, n, o, d, tmin, tmax, hit, order, s->d_fetch.p, s->count_visits ? s->d_counters.p : nullptr, lc, st);
     return trace_end(s, n, true, st);
 }
 
@@ -530,6 +589,7 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     rcn.scale = 1.0 / params->samples_per_pixel;
     for (int k = 0; k < 3; ++k) rcn.background[k] = params->background[k];
     rcn.rng_key = params->rng_key;
+    for (int k = 0; k < 3; ++k) { rcn.key_lo[k] = s->key_lo[k]; rcn.key_scale[k] = s->key_scale[k]; }
 
     const int64_t budget = pass_path_budget();
     int per_pass = (int)std::max<int64_t>(1, budget / rcn.npix);

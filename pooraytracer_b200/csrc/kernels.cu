@@ -23,6 +23,7 @@
 #include <cuda_runtime.h>
 #include <float.h>
 
+#include <algorithm>
 #include <unordered_map>
 
 #include "../../include/prt_b200.h"
@@ -79,6 +80,91 @@ __device__ __forceinline__ void flush_counters(const VisitCounters& c, unsigned 
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * ray binning (launch.h): key, scan, scatter
+ * ---------------------------------------------------------------------------------------------- */
+__device__ __forceinline__ uint32_t spread3(uint32_t v) { /* 4 bits -> every third bit */
+    v = (v | (v << 4)) & 0x0c3u;
+    v = (v | (v << 2)) & 0x249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t ray_key(const float* lo, const float* scale, d3 o, d3 d) {
+    const float G = (float)(PRT_KEY_GRID - 1);
+    /* fminf / fmaxf drop a NaN coordinate: such a ray lands in cell 0, which is as good as any */
+    const uint32_t ix = (uint32_t)fminf(fmaxf(((float)o.x - lo[0]) * scale[0], 0.f), G);
+    const uint32_t iy = (uint32_t)fminf(fmaxf(((float)o.y - lo[1]) * scale[1], 0.f), G);
+    const uint32_t iz = (uint32_t)fminf(fmaxf(((float)o.z - lo[2]) * scale[2], 0.f), G);
+    const uint32_t oct = (d.x < 0.0 ? 1u : 0u) | (d.y < 0.0 ? 2u : 0u) | (d.z < 0.0 ? 4u : 0u);
+    return ((spread3(ix) | (spread3(iy) << 1) | (spread3(iz) << 2)) << 3) | oct;
+}
+
+/* one block per histogram: exclusive scan of hist -> cursor, hist zeroed for its next use */
+__global__ void __launch_bounds__(1024) k_sort_scan(int32_t* __restrict__ hist, int32_t* __restrict__ cursor) {
+    constexpr int PER = PRT_KEY_BINS / 1024;
+    __shared__ int32_t warp_sum[32];
+    int32_t* h = hist + (size_t)blockIdx.x * PRT_KEY_BINS;
+    int32_t* c = cursor + (size_t)blockIdx.x * PRT_KEY_BINS;
+    int32_t v[PER];
+    int32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        v[k] = h[threadIdx.x * PER + k];
+        sum += v[k];
+    }
+    int32_t incl = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane_id() >= o) incl += up;
+    }
+    if (lane_id() == 31) warp_sum[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int32_t w = warp_sum[threadIdx.x];
+        for (int o = 1; o < 32; o <<= 1) {
+            const int32_t up = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane_id() >= o) w += up;
+        }
+        warp_sum[threadIdx.x] = w;
+    }
+    __syncthreads();
+    int32_t run = incl - sum + ((threadIdx.x >> 5) ? warp_sum[(threadIdx.x >> 5) - 1] : 0);
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        c[threadIdx.x * PER + k] = run;
+        run += v[k];
+        h[threadIdx.x * PER + k] = 0;
+    }
+}
+
+/* out[cursor[key]++] = in[qi] (in == nullptr: the identity). blockIdx.y picks the queue. */
+struct SortJob {
+    const int32_t* n;  /* queue length on the device (nullptr: n_host) */
+    int32_t n_host;
+    const uint16_t* keys;
+    const int32_t* in;
+    int32_t* out;
+};
+__global__ void __launch_bounds__(256) k_sort_scatter(SortJob j0, SortJob j1, int32_t* __restrict__ cursor) {
+    const SortJob j = blockIdx.y == 0 ? j0 : j1;
+    int32_t* c = cursor + (size_t)blockIdx.y * PRT_KEY_BINS;
+    const int32_t n = j.n ? *j.n : j.n_host;
+    for (int32_t qi = blockIdx.x * blockDim.x + threadIdx.x; qi < n; qi += gridDim.x * blockDim.x) {
+        const int32_t pos = atomicAdd(c + j.keys[qi], 1);
+        j.out[pos] = j.in ? j.in[qi] : qi;
+    }
+}
+
+/* keys + histogram of a ray-query batch */
+struct KeyBox { float lo[3], scale[3]; };
+__global__ void __launch_bounds__(256) k_query_keys(int64_t n, const double* __restrict__ o, const double* __restrict__ d, KeyBox kb,
+                                                    uint16_t* __restrict__ keys, int32_t* __restrict__ hist) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t k = ray_key(kb.lo, kb.scale, mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+        keys[i] = (uint16_t)k;
+        atomicAdd(hist + k, 1);
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
  * ray queries
  * ---------------------------------------------------------------------------------------------- */
 struct ClosestQueryPolicy {
@@ -86,7 +172,8 @@ struct ClosestQueryPolicy {
     int32_t* prim;
     double *t, *alpha, *beta;
     const int32_t* slot_prim;
-    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return qi; }
+    const int32_t* __restrict__ order; /* binned ray order, or nullptr */
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return order ? order[qi] : qi; }
     __device__ __forceinline__ void prefetch(int32_t i) const {
         prefetch_l2(o + 3 * (int64_t)i);
         prefetch_l2(d + 3 * (int64_t)i);
@@ -110,7 +197,8 @@ struct ClosestQueryPolicy {
 struct AnyQueryPolicy {
     const double *o, *d, *tmin, *tmax;
     uint8_t* hit;
-    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return qi; }
+    const int32_t* __restrict__ order;
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return order ? order[qi] : qi; }
     __device__ __forceinline__ void prefetch(int32_t i) const {
         prefetch_l2(o + 3 * (int64_t)i);
         prefetch_l2(d + 3 * (int64_t)i);
@@ -132,9 +220,9 @@ template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                        const double* __restrict__ tmin, const double* __restrict__ tmax,
                                                        int32_t* __restrict__ prim, double* __restrict__ t, double* __restrict__ alpha,
-                                                       double* __restrict__ beta, int32_t* fetch, unsigned long long* counters) {
+                                                       double* __restrict__ beta, const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
     VisitCounters cnt = {0, 0};
-    ClosestQueryPolicy pol = {o, d, tmin, tmax, prim, t, alpha, beta, S.slot_prim};
+    ClosestQueryPolicy pol = {o, d, tmin, tmax, prim, t, alpha, beta, S.slot_prim, order};
     traverse_persistent<false, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
 }
@@ -142,9 +230,9 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                    const double* __restrict__ tmin, const double* __restrict__ tmax, uint8_t* __restrict__ hit,
-                                                   int32_t* fetch, unsigned long long* counters) {
+                                                   const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
     VisitCounters cnt = {0, 0};
-    AnyQueryPolicy pol = {o, d, tmin, tmax, hit};
+    AnyQueryPolicy pol = {o, d, tmin, tmax, hit, order};
     traverse_persistent<true, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
 }
@@ -185,7 +273,21 @@ __device__ __forceinline__ void camera_ray(const RenderConst& rc, int32_t slot, 
  * finishes it an event later, when the atomic's round trip to L2 has long been paid */
 struct DeferredPush {
     int32_t cls, slot, raw;
-    __device__ __forceinline__ void init() { cls = -1; slot = 0; raw = 0; }
+    uint32_t key; /* ray-binning key of the pushed ray (used by complete_keyed only) */
+    __device__ __forceinline__ void init() { cls = -1; slot = 0; raw = 0; key = 0; }
+    /* single queue + its key array: the entry and its key land at the same index */
+    __device__ __forceinline__ void complete_keyed(int32_t* queue, uint16_t* keys) {
+        const unsigned mask = __ballot_sync(0xffffffffu, cls == 0);
+        if (mask != 0) {
+            const int32_t base = __shfl_sync(0xffffffffu, raw, __ffs(mask) - 1);
+            if (cls == 0) {
+                const int32_t at = base + __popc(mask & ((1u << lane_id()) - 1u));
+                queue[at] = slot;
+                keys[at] = (uint16_t)key;
+            }
+        }
+        cls = -1;
+    }
     template <int NQ>
     __device__ __forceinline__ void issue(int32_t* const (&counters)[NQ], int c, int32_t s) {
         cls = c;
@@ -296,11 +398,11 @@ struct ExtendPolicy {
 };
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce) {
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = bounce == 0 ? rc.n_paths : ctrl->n_extend;
     VisitCounters cnt = {0, 0};
-    ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, pb.q_extend[bounce & 1], bounce, {-1, 0, 0}};
+    ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, sorted ? pb.qs_extend : pb.q_extend[bounce & 1], bounce, {-1, 0, 0, 0}};
     traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_extend, n, cnt);
     flush_counters<COUNT>(cnt, pb.counters);
 }
@@ -319,7 +421,7 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScen
 #define PRT_SHADE_DEFER 0
 #endif
 template <int CLS>
-__global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
+__global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sort) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     BounceCtrl* next = pb.ctrl + bounce + 1;
     const int32_t n = ctrl->n_mat[CLS];
@@ -336,6 +438,7 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
     push_extend.init();
     for (; qi < n_round; qi += stride) {
         bool want_shadow = false, want_extend = false;
+        uint32_t key_shadow = 0, key_extend = 0;
         const int32_t slot = slot_next;
         slot_next = slot_next2;
         slot_next2 = (int64_t)qi + 2 * (int64_t)stride < n ? queue[qi + 2 * stride] : -1;
@@ -390,6 +493,7 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
                     r->sdist = distance;
                     st3(r->scontrib, T * direct);
                     want_shadow = true;
+                    if (sort) key_shadow = ray_key(rc.key_lo, rc.key_scale, s.position, light_dir);
                 }
             }
             /* ---- Russian roulette + BSDF sampling (Camera.cpp:176-201) ---- */
@@ -408,6 +512,7 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
                     r->dim = rng.dim;
                     r->flags = m.skip_light_sampling ? PRT_FLAG_PREV_SKIP : 0u;
                     want_extend = true;
+                    if (sort) key_extend = ray_key(rc.key_lo, rc.key_scale, s.position, out_dir);
                 }
             }
             if (want_shadow && !want_extend) st3(r->o, s.position); /* shadow ray origin */
@@ -426,8 +531,18 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
 #else
             push_shadow.issue(n0, want_shadow ? 0 : -1, slot);
             push_extend.issue(n1, want_extend ? 0 : -1, slot);
-            push_shadow.complete(q0);
-            push_extend.complete(q1);
+            if (sort) {
+                /* histogram of the keys: fire-and-forget REDs, consumed by k_sort_scan */
+                if (want_shadow) atomicAdd(pb.hist + PRT_KEY_BINS + key_shadow, 1);
+                if (want_extend) atomicAdd(pb.hist + key_extend, 1);
+                push_shadow.key = key_shadow;
+                push_extend.key = key_extend;
+                push_shadow.complete_keyed(out_q[0], pb.key_shadow);
+                push_extend.complete_keyed(out_q[1], pb.key_extend);
+            } else {
+                push_shadow.complete(q0);
+                push_extend.complete(q1);
+            }
 #endif
         }
     }
@@ -483,15 +598,15 @@ struct ShadowPolicy {
 };
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce) {
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = ctrl->n_shadow;
     VisitCounters cnt = {0, 0};
     if (rc.flags & PRT_RENDER_EXACT_VISIBILITY) {
-        ShadowPolicy<true> pol = {pb, pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
+        ShadowPolicy<true> pol = {pb, sorted ? pb.qs_shadow : pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
         traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
     } else {
-        ShadowPolicy<false> pol = {pb, pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
+        ShadowPolicy<false> pol = {pb, sorted ? pb.qs_shadow : pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
         traverse_persistent<true, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
     }
     flush_counters<COUNT>(cnt, pb.counters);
@@ -590,15 +705,28 @@ static int persistent_grid(K kernel, int block, const LaunchConfig& lc, int64_t 
     } while (0)
 
 void launch_trace_closest(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
-                          int32_t* prim, double* t, double* alpha, double* beta, int32_t* fetch, unsigned long long* counters,
-                          const LaunchConfig& lc, cudaStream_t st) {
+                          int32_t* prim, double* t, double* alpha, double* beta, const int32_t* order, int32_t* fetch,
+                          unsigned long long* counters, const LaunchConfig& lc, cudaStream_t st) {
     if (n <= 0) return;
-    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_closest, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, prim, t, alpha, beta, fetch, counters));
+    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_closest, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, prim, t, alpha, beta, order, fetch, counters));
 }
 void launch_trace_any(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
-                      uint8_t* hit, int32_t* fetch, unsigned long long* counters, const LaunchConfig& lc, cudaStream_t st) {
+                      uint8_t* hit, const int32_t* order, int32_t* fetch, unsigned long long* counters, const LaunchConfig& lc,
+                      cudaStream_t st) {
     if (n <= 0) return;
-    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_any, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, hit, fetch, counters));
+    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_any, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, hit, order, fetch, counters));
+}
+void launch_query_sort(int64_t n, const double* o, const double* d, const float* key_lo, const float* key_scale, uint16_t* keys,
+                       int32_t* hist, int32_t* cursor, int32_t* order, const LaunchConfig& lc, cudaStream_t st) {
+    if (n <= 0) return;
+    KeyBox kb;
+    for (int k = 0; k < 3; ++k) { kb.lo[k] = key_lo[k]; kb.scale[k] = key_scale[k]; }
+    const int64_t want = (n + 255) / 256, cap = (int64_t)lc.sm_count * 8;
+    const unsigned grid = (unsigned)(want < cap ? want : cap);
+    k_query_keys<<<grid, 256, 0, st>>>(n, o, d, kb, keys, hist);
+    k_sort_scan<<<1, 1024, 0, st>>>(hist, cursor);
+    SortJob j = {nullptr, (int32_t)n, keys, nullptr, order};
+    k_sort_scatter<<<dim3(grid, 1), 256, 0, st>>>(j, j, cursor);
 }
 void launch_sample_lights(const DevScene& S, int64_t n, const double* origins, const double* u, double* position, double* normal,
                           uint8_t* front, double* pdf, int32_t* prim, cudaStream_t st) {
@@ -620,23 +748,40 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR>, 128, shade_lc, rc.n_paths);
     const int g_shade3 = persistent_grid(k_shade<CLS_COOK>, 128, shade_lc, rc.n_paths);
     cudaEvent_t* ev = lc.stage_events;
+    /* ray binning is decided here, per bounce, from the expected queue length: Russian roulette thins
+     * the wavefront geometrically, and reordering a short queue costs more launches than it saves */
+    const double survive = rc.rr < 1.0 ? (rc.rr > 0.0 ? rc.rr : 0.0) : 1.0;
+    double expect = (double)rc.n_paths;
+    int sorted = 0; /* this bounce's extend queue was reordered by the previous bounce */
+    const int sort_grid = (int)std::min<int64_t>((rc.n_paths + 255) / 256, (int64_t)lc.sm_count * 8);
     for (int b = 0; b < n_bounces; ++b) {
+        const int sort = lc.sort_min > 0 && expect >= (double)lc.sort_min ? 1 : 0;
         if (ev) cudaEventRecord(ev[4 * b], st);
-        PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, prim_class, rc, pb, b));
+        PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, prim_class, rc, pb, b, sorted));
         if (ev) cudaEventRecord(ev[4 * b + 1], st);
-        k_shade<CLS_LAMBERT><<<g_shade0, 128, 0, st>>>(S, rc, pb, b);
-        k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b);
-        k_shade<CLS_MIRROR><<<g_shade2, 128, 0, st>>>(S, rc, pb, b);
+        k_shade<CLS_LAMBERT><<<g_shade0, 128, 0, st>>>(S, rc, pb, b, sort);
+        k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b, sort);
+        k_shade<CLS_MIRROR><<<g_shade2, 128, 0, st>>>(S, rc, pb, b, sort);
         launches += 4;
         if (rc.has_cook) {
-            k_shade<CLS_COOK><<<g_shade3, 128, 0, st>>>(S, rc, pb, b);
+            k_shade<CLS_COOK><<<g_shade3, 128, 0, st>>>(S, rc, pb, b, sort);
             ++launches;
+        }
+        if (sort) {
+            BounceCtrl* dc = pb.ctrl + b;
+            const SortJob je = {&(dc + 1)->n_extend, 0, pb.key_extend, pb.q_extend[(b + 1) & 1], pb.qs_extend};
+            const SortJob js = {&dc->n_shadow, 0, pb.key_shadow, pb.q_shadow, pb.qs_shadow};
+            k_sort_scan<<<2, 1024, 0, st>>>(pb.hist, pb.cursor);
+            k_sort_scatter<<<dim3(sort_grid, 2), 256, 0, st>>>(je, js, pb.cursor);
+            launches += 2;
         }
         if (ev) cudaEventRecord(ev[4 * b + 2], st);
         if (rc.sample_lights) {
-            PRT_DISPATCH(count, wide, k_shadow, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, rc, pb, b));
+            PRT_DISPATCH(count, wide, k_shadow, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, rc, pb, b, sort));
             ++launches;
         }
+        sorted = sort;
+        expect *= survive;
         if (ev) cudaEventRecord(ev[4 * b + 3], st);
     }
     k_accumulate<<<(rc.npix + 255) / 256 < lc.sm_count * 8 ? (rc.npix + 255) / 256 : lc.sm_count * 8, 256, 0, st>>>(rc, pb, rgb);

@@ -186,6 +186,35 @@ def test_render_modes_agree(gpu_ctx):
     assert np.array_equal(s.render(cam, prm), base)
 
 
+@pytest.mark.parametrize("accel", [capi.ACCEL_SAH_BVH2, capi.ACCEL_SAH_BVH4])
+def test_ray_binning_changes_nothing(gpu_ctx, accel, monkeypatch):
+    """PRT_SORT_MIN: the counting sort of the ray queues (and of query batches) reorders work only.
+    Forced on for every queue (1) and off (0): ray queries and images are bit-identical, and the
+    forced-on run still matches the reference golden."""
+    sc, o, d = scene_and_rays("cornell")
+    g = gold("rays_cornell.npz")
+    s = Scene(gpu_ctx, sc, accel=accel)
+    rsc, cam, prm = _render_case("cornell_nee")
+    rs = Scene(gpu_ctx, rsc, accel=accel)
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("PRT_SORT_MIN", mode)
+        out[mode] = (s.trace_closest(o, d, 1e-4, np.inf), s.trace_any(o, d, 1e-3, g["tmax"]), rs.render(cam, prm))
+    monkeypatch.delenv("PRT_SORT_MIN")
+    for a, b in zip(out["0"][0], out["1"][0]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(out["1"][0][0], g["prim"]) and np.array_equal(out["1"][0][1], g["t"])
+    assert np.array_equal(out["0"][1], out["1"][1])
+    assert np.array_equal(out["0"][2], out["1"][2])
+    _compare_images(out["1"][2], gold("render_cornell_nee.npz")["image"], "cornell_nee binned")
+    # rays far outside the scene box, NaN / inf coordinates: the key clamps, nothing is lost
+    monkeypatch.setenv("PRT_SORT_MIN", "1")
+    o2 = o.copy(); o2[::7] *= 1e6; o2[3] = [np.nan, 0, 0]; o2[5] = [np.inf, -np.inf, 0]
+    p_on = s.trace_closest(o2, d, 1e-4, np.inf)[0]
+    monkeypatch.setenv("PRT_SORT_MIN", "0")
+    assert np.array_equal(p_on, s.trace_closest(o2, d, 1e-4, np.inf)[0])
+
+
 def test_resolve_matches_reference_quantiser(gpu_ctx):
     import torch
     sc, cam, prm = _render_case("tiny_nee")

@@ -25,7 +25,7 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--check", type=int, default=0, help="compare the first N rays with the CPU oracle")
     ap.add_argument("--max-leaf", type=int, default=0)
-    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh2"), choices=["bvh2", "bvh4"])
+    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4"])
     a = ap.parse_args()
     import torch
     from pooraytracer_b200 import Context, Scene, _capi as capi, scenes
