@@ -98,6 +98,7 @@ struct prt_scene {
     DevBuf<double> d_srgb;
     DevBuf<uint8_t> d_prim_class;
     bool has_cook = false;
+    int class_mask = 0;
     DevScene dev;
 
     /* scratch for the host-pointer entry points */
@@ -157,6 +158,9 @@ LaunchConfig launch_config(const prt_context* ctx) {
      * traversal time and cost more than that in histogram atomics and the scatter pass */
     env = std::getenv("PRT_SORT_MIN");
     lc.sort_min = env ? std::max<int64_t>(0, std::atoll(env)) : 0;
+    /* PRT_TAIL_PATHS: see LaunchConfig::tail_paths */
+    env = std::getenv("PRT_TAIL_PATHS");
+    lc.tail_paths = env ? std::max<int64_t>(0, std::atoll(env)) : 262144;
     return lc;
 }
 
@@ -353,6 +357,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     cudaStream_t st = s->ctx->stream;
     std::vector<uint8_t> prim_class((size_t)h.n_tris);
     s->has_cook = false;
+    s->class_mask = 0;
     for (int64_t p = 0; p < h.n_tris; ++p) {
         const DevMaterial& m = h.dev_materials[h.shade[p].material];
         uint8_t c;
@@ -365,6 +370,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
         else c = CLS_LAMBERT; /* unknown types fall back to Lambertian like Model.cpp:282-285 */
         prim_class[p] = c;
         if (c == CLS_COOK) s->has_cook = true;
+        if (c < CLS_SHADED) s->class_mask |= 1 << c;
     }
     std::vector<double> lut(h.srgb_lut, h.srgb_lut + 256);
     CUDA_TRY(s->d_tris.upload(h.isect_slots, st));
@@ -584,6 +590,7 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     rcn.max_depth = params->max_depth;
     rcn.sample_lights = params->sample_lights ? 1 : 0;
     rcn.has_cook = s->has_cook ? 1 : 0;
+    rcn.class_mask = s->class_mask;
     rcn.flags = params->flags | (s->count_visits ? PRT_RENDER_COUNTERS : 0u);
     rcn.rr = params->russian_roulette;
     rcn.scale = 1.0 / params->samples_per_pixel;
@@ -618,11 +625,17 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
         rcn.sample_first = s0;
         rcn.n_samples = std::min(per_pass, se - s0);
         rcn.n_paths = rcn.n_samples * rcn.npix;
-        launches += (uint64_t)launch_render_pass(s->dev, s->d_prim_class.p, rcn, pb, rgb_device, s->d_counters.p, lc, st);
+        int tail_first = n_bounces;
+        launches += (uint64_t)launch_render_pass(s->dev, s->d_prim_class.p, rcn, pb, rgb_device, s->d_counters.p, lc, st, &tail_first);
         CUDA_TRY(cudaGetLastError());
         if (stage_timing) {
             CUDA_TRY(cudaStreamSynchronize(st));
-            for (int b = 0; b < n_bounces; ++b) {
+            if (tail_first < n_bounces) { /* the tail launch (all stages of the late bounces) is booked as traversal */
+                float a = 0.f;
+                cudaEventElapsedTime(&a, lc.stage_events[4 * tail_first], lc.stage_events[4 * tail_first + 1]);
+                extend_ms += a;
+            }
+            for (int b = 0; b < tail_first; ++b) {
                 float a = 0.f, c = 0.f, d = 0.f;
                 cudaEventElapsedTime(&a, lc.stage_events[4 * b], lc.stage_events[4 * b + 1]);
                 cudaEventElapsedTime(&c, lc.stage_events[4 * b + 1], lc.stage_events[4 * b + 2]);

@@ -20,6 +20,7 @@
  * Compiled with -fmad=false: FP64 results must carry the reference's bits, and its x86-64 objects
  * contain no fused multiply-add.
  */
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <float.h>
 
@@ -37,6 +38,8 @@
 #ifndef PRT_TRAVERSE_MIN_BLOCKS
 #define PRT_TRAVERSE_MIN_BLOCKS 6
 #endif
+
+namespace cg = cooperative_groups;
 
 namespace prt {
 
@@ -321,10 +324,10 @@ struct ExtendPolicy {
     const RenderConst& rc;
     const PathBuffers& pb;
     BounceCtrl* ctrl;
-    const int32_t* __restrict__ queue;
+    const int32_t* queue; /* read with ld.cg: k_tail rewrites the queues inside one launch */
     int bounce;
     DeferredPush push;
-    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return bounce == 0 ? qi : queue[qi]; }
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return bounce == 0 ? qi : __ldcg(queue + qi); }
     __device__ __forceinline__ void prefetch(int32_t slot) const {
         if (bounce != 0) prefetch_l2(pb.rec + slot);
     }
@@ -398,12 +401,18 @@ struct ExtendPolicy {
 };
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+__device__ __forceinline__ void extend_body(const DevScene& S, const uint8_t* __restrict__ prim_class, const RenderConst& rc, const PathBuffers& pb,
+                                            int bounce, int sorted, VisitCounters& cnt) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
-    const int32_t n = bounce == 0 ? rc.n_paths : ctrl->n_extend;
-    VisitCounters cnt = {0, 0};
+    const int32_t n = bounce == 0 ? rc.n_paths : __ldcg(&ctrl->n_extend);
     ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, sorted ? pb.qs_extend : pb.q_extend[bounce & 1], bounce, {-1, 0, 0, 0}};
     traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_extend, n, cnt);
+}
+
+template <bool COUNT, int WIDE>
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+    VisitCounters cnt = {0, 0};
+    extend_body<COUNT, WIDE>(S, prim_class, rc, pb, bounce, sorted, cnt);
     flush_counters<COUNT>(cnt, pb.counters);
 }
 
@@ -421,18 +430,18 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScen
 #define PRT_SHADE_DEFER 0
 #endif
 template <int CLS>
-__global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sort) {
+__device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     BounceCtrl* next = pb.ctrl + bounce + 1;
-    const int32_t n = ctrl->n_mat[CLS];
-    const int32_t* __restrict__ queue = pb.q_mat[CLS];
+    const int32_t n = __ldcg(&ctrl->n_mat[CLS]);
+    const int32_t* queue = pb.q_mat[CLS]; /* ld.cg, as in ExtendPolicy */
     int32_t* const out_q[2] = {pb.q_shadow, pb.q_extend[(bounce + 1) & 1]};
     int32_t* const out_n[2] = {&ctrl->n_shadow, &next->n_extend};
     const int32_t n_round = (n + 31) & ~31;
     const int32_t stride = gridDim.x * blockDim.x;
     int32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
-    int32_t slot_next = qi < n ? queue[qi] : -1;
-    int32_t slot_next2 = qi + stride < n ? queue[qi + stride] : -1;
+    int32_t slot_next = qi < n ? __ldcg(queue + qi) : -1;
+    int32_t slot_next2 = qi + stride < n ? __ldcg(queue + qi + stride) : -1;
     DeferredPush push_shadow, push_extend;
     push_shadow.init();
     push_extend.init();
@@ -441,7 +450,7 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
         uint32_t key_shadow = 0, key_extend = 0;
         const int32_t slot = slot_next;
         slot_next = slot_next2;
-        slot_next2 = (int64_t)qi + 2 * (int64_t)stride < n ? queue[qi + 2 * stride] : -1;
+        slot_next2 = (int64_t)qi + 2 * (int64_t)stride < n ? __ldcg(queue + qi + 2 * stride) : -1;
 #if PRT_SHADE_PREFETCH
         if (slot_next >= 0) {
             prefetch_l2(pb.rec + slot_next);
@@ -554,6 +563,11 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
     }
 }
 
+template <int CLS>
+__global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sort) {
+    shade_body<CLS>(S, rc, pb, bounce, sort);
+}
+
 /* NEE visibility (Camera.cpp:143-155). The reference asks for the closest hit on [1e-3, DBL_MAX]
  * along the unit light direction and accepts iff something was hit and
  * distance - |ps - hit| < 1e-3, i.e. iff no surface lies closer than distance - 1e-3: an any-hit
@@ -561,10 +575,10 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
 template <bool EXACT>
 struct ShadowPolicy {
     const PathBuffers& pb;
-    const int32_t* __restrict__ queue;
+    const int32_t* queue;
     d3 ps, dir;
     double distance;
-    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return queue[qi]; }
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return __ldcg(queue + qi); }
     __device__ __forceinline__ void prefetch(int32_t slot) const {
         prefetch_l2(pb.rec + slot);
         prefetch_l2(reinterpret_cast<const char*>(pb.rec + slot) + 128);
@@ -598,16 +612,50 @@ struct ShadowPolicy {
 };
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+__device__ __forceinline__ void shadow_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sorted, VisitCounters& cnt) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
-    const int32_t n = ctrl->n_shadow;
-    VisitCounters cnt = {0, 0};
+    const int32_t n = __ldcg(&ctrl->n_shadow);
     if (rc.flags & PRT_RENDER_EXACT_VISIBILITY) {
         ShadowPolicy<true> pol = {pb, sorted ? pb.qs_shadow : pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
         traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
     } else {
         ShadowPolicy<false> pol = {pb, sorted ? pb.qs_shadow : pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
         traverse_persistent<true, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
+    }
+}
+
+template <bool COUNT, int WIDE>
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+    VisitCounters cnt = {0, 0};
+    shadow_body<COUNT, WIDE>(S, rc, pb, bounce, sorted, cnt);
+    flush_counters<COUNT>(cnt, pb.counters);
+}
+
+/* The tail of a pass in ONE cooperative launch. Russian roulette thins the wavefront geometrically
+ * (rr 0.8, depth 100: bounce 27 holds < 0.3 % of the paths), and a bounce of a few thousand rays
+ * costs what its dependent chain of launches and memory latencies costs, not what its rays cost:
+ * the ncu launch list of the per-bounce pipeline shows bounces 30..100 at 30-80 us each per stage
+ * (profiles/r1_s5_launches.csv). From bounce `first` on, the same stage bodies run back to back
+ * inside this kernel, separated by grid-wide barriers, until the extend queue is empty. Results are
+ * those of the per-bounce launches (same code, same queues); only launch count and idle time change.
+ * The barrier after the shadow stage is needed: shadow(b) and extend(b + 1) both update rec.L. */
+template <bool COUNT, int WIDE>
+__global__ void __launch_bounds__(128, 2) k_tail(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int first) {
+    cg::grid_group grid = cg::this_grid();
+    VisitCounters cnt = {0, 0};
+    for (int b = first; b <= rc.max_depth; ++b) {
+        if (b > 0 && __ldcg(&pb.ctrl[b].n_extend) == 0) break; /* uniform: written before the last barrier */
+        extend_body<COUNT, WIDE>(S, prim_class, rc, pb, b, 0, cnt);
+        grid.sync();
+        if (rc.class_mask & (1 << CLS_LAMBERT)) shade_body<CLS_LAMBERT>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_PHONG)) shade_body<CLS_PHONG>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_MIRROR)) shade_body<CLS_MIRROR>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_COOK)) shade_body<CLS_COOK>(S, rc, pb, b, 0);
+        grid.sync();
+        if (rc.sample_lights) {
+            shadow_body<COUNT, WIDE>(S, rc, pb, b, 0, cnt);
+            grid.sync();
+        }
     }
     flush_counters<COUNT>(cnt, pb.counters);
 }
@@ -735,7 +783,7 @@ void launch_sample_lights(const DevScene& S, int64_t n, const double* origins, c
 }
 
 int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const RenderConst& rc, const PathBuffers& pb, double* rgb,
-                       unsigned long long* totals, const LaunchConfig& lc, cudaStream_t st) {
+                       unsigned long long* totals, const LaunchConfig& lc, cudaStream_t st, int* tail_first_out) {
     int launches = 0;
     const int n_bounces = rc.max_depth + 1;
     cudaMemsetAsync(pb.ctrl, 0, sizeof(BounceCtrl) * (size_t)(n_bounces + 1), st);
@@ -748,25 +796,27 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR>, 128, shade_lc, rc.n_paths);
     const int g_shade3 = persistent_grid(k_shade<CLS_COOK>, 128, shade_lc, rc.n_paths);
     cudaEvent_t* ev = lc.stage_events;
-    /* ray binning is decided here, per bounce, from the expected queue length: Russian roulette thins
-     * the wavefront geometrically, and reordering a short queue costs more launches than it saves */
+    /* Both per-bounce decisions are taken here from the EXPECTED queue length n_paths * rr^bounce
+     * (Russian roulette thins the wavefront geometrically; the host never reads a queue length back):
+     *   - ray binning for long queues (off by default, launch.h);
+     *   - the first bounce of the tail: once fewer than lc.tail_paths paths are expected, the rest of
+     *     the pass runs inside ONE cooperative launch (k_tail). */
     const double survive = rc.rr < 1.0 ? (rc.rr > 0.0 ? rc.rr : 0.0) : 1.0;
     double expect = (double)rc.n_paths;
     int sorted = 0; /* this bounce's extend queue was reordered by the previous bounce */
     const int sort_grid = (int)std::min<int64_t>((rc.n_paths + 255) / 256, (int64_t)lc.sm_count * 8);
-    for (int b = 0; b < n_bounces; ++b) {
+    int b = 0;
+    for (; b < n_bounces; ++b) {
+        if (lc.tail_paths > 0 && expect < (double)lc.tail_paths) break;
         const int sort = lc.sort_min > 0 && expect >= (double)lc.sort_min ? 1 : 0;
         if (ev) cudaEventRecord(ev[4 * b], st);
         PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, prim_class, rc, pb, b, sorted));
+        ++launches;
         if (ev) cudaEventRecord(ev[4 * b + 1], st);
-        k_shade<CLS_LAMBERT><<<g_shade0, 128, 0, st>>>(S, rc, pb, b, sort);
-        k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b, sort);
-        k_shade<CLS_MIRROR><<<g_shade2, 128, 0, st>>>(S, rc, pb, b, sort);
-        launches += 4;
-        if (rc.has_cook) {
-            k_shade<CLS_COOK><<<g_shade3, 128, 0, st>>>(S, rc, pb, b, sort);
-            ++launches;
-        }
+        if (rc.class_mask & (1 << CLS_LAMBERT)) { k_shade<CLS_LAMBERT><<<g_shade0, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+        if (rc.class_mask & (1 << CLS_PHONG)) { k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+        if (rc.class_mask & (1 << CLS_MIRROR)) { k_shade<CLS_MIRROR><<<g_shade2, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+        if (rc.class_mask & (1 << CLS_COOK)) { k_shade<CLS_COOK><<<g_shade3, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
         if (sort) {
             BounceCtrl* dc = pb.ctrl + b;
             const SortJob je = {&(dc + 1)->n_extend, 0, pb.key_extend, pb.q_extend[(b + 1) & 1], pb.qs_extend};
@@ -783,6 +833,38 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         sorted = sort;
         expect *= survive;
         if (ev) cudaEventRecord(ev[4 * b + 3], st);
+    }
+    if (tail_first_out) *tail_first_out = b;
+    if (b < n_bounces) {
+        /* the tail: bounces b .. max_depth in one cooperative launch (its time is booked as traversal
+         * time by the stage timing: events 4b, 4b + 1) */
+        if (ev) cudaEventRecord(ev[4 * b], st);
+        int first = b;
+        DevScene S_ = S;
+        RenderConst rc_ = rc;
+        PathBuffers pb_ = pb;
+        const uint8_t* pc_ = prim_class;
+        void* args[] = {(void*)&S_, (void*)&pc_, (void*)&rc_, (void*)&pb_, (void*)&first};
+        const void* fn = count ? (wide ? (const void*)k_tail<true, 4> : (const void*)k_tail<true, 2>)
+                               : (wide ? (const void*)k_tail<false, 4> : (const void*)k_tail<false, 2>);
+        static std::unordered_map<const void*, int> occ;
+        int per_sm;
+        auto it = occ.find(fn);
+        if (it == occ.end()) {
+            per_sm = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 128, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+            occ[fn] = per_sm;
+        } else {
+            per_sm = it->second;
+        }
+        if (per_sm > 2) per_sm = 2;
+        int64_t want = (rc.n_paths + 127) / 128;
+        const int64_t cap = (int64_t)per_sm * lc.sm_count;
+        if (want > cap) want = cap;
+        if (want < 1) want = 1;
+        cudaLaunchCooperativeKernel(fn, dim3((unsigned)want), dim3(128), args, 0, st);
+        ++launches;
+        if (ev) cudaEventRecord(ev[4 * b + 1], st);
     }
     k_accumulate<<<(rc.npix + 255) / 256 < lc.sm_count * 8 ? (rc.npix + 255) / 256 : lc.sm_count * 8, 256, 0, st>>>(rc, pb, rgb);
     k_pass_stats<<<1, 32, 0, st>>>(pb.ctrl, n_bounces, rc.n_paths, totals);

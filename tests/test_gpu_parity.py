@@ -149,9 +149,17 @@ def _compare_images(img, ref, what):
     return frac_tight, rmse
 
 
+# PRT_TAIL_PATHS: "0" = one launch per stage and bounce; "1500" = the cooperative tail kernel takes over
+# part-way down the path (these frames hold 1.2-6 k paths); None = the default, under which frames this
+# small run wholly inside the tail kernel
+@pytest.mark.parametrize("tail", ["0", "1500", None])
 @pytest.mark.parametrize("accel", ACCELS)
 @pytest.mark.parametrize("name", list(cases.RENDER_CASES))
-def test_render_vs_reference_golden(gpu_ctx, name, accel):
+def test_render_vs_reference_golden(gpu_ctx, name, accel, tail, monkeypatch):
+    if tail is None:
+        monkeypatch.delenv("PRT_TAIL_PATHS", raising=False)
+    else:
+        monkeypatch.setenv("PRT_TAIL_PATHS", tail)
     sc, cam, prm = _render_case(name)
     g = gold(f"render_{name}.npz")
     s = Scene(gpu_ctx, sc, accel=accel)
@@ -184,6 +192,16 @@ def test_render_modes_agree(gpu_ctx):
     assert np.array_equal(multi, base)
     # determinism
     assert np.array_equal(s.render(cam, prm), base)
+    # per-bounce launches, hand-over to the tail kernel at various bounces: the same bits
+    for tail in ("0", "3000", "1000", "100", "1000000000"):
+        os.environ["PRT_TAIL_PATHS"] = tail
+        try:
+            img = s.render(cam, prm)
+            st = s.stats()
+        finally:
+            del os.environ["PRT_TAIL_PATHS"]
+        assert np.array_equal(img, base), f"PRT_TAIL_PATHS={tail} changes the image"
+        assert st.extend_rays + st.shadow_rays > 0
 
 
 @pytest.mark.parametrize("accel", [capi.ACCEL_SAH_BVH2, capi.ACCEL_SAH_BVH4])
