@@ -429,6 +429,9 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScen
 #ifndef PRT_SHADE_DEFER
 #define PRT_SHADE_DEFER 0
 #endif
+#ifndef PRT_SHADE_PIPE
+#define PRT_SHADE_PIPE 0 /* measured: shade 8.36 ms against 7.90 ms unpipelined (profiles/r1_s8_ab.txt) */
+#endif
 template <int CLS>
 __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
@@ -442,6 +445,17 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
     int32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
     int32_t slot_next = qi < n ? __ldcg(queue + qi) : -1;
     int32_t slot_next2 = qi + stride < n ? __ldcg(queue + qi + stride) : -1;
+#if PRT_SHADE_PIPE
+    /* software pipeline over the dependent chain queue -> record -> triangle -> material (half of the
+     * long-scoreboard samples of the unpipelined loop, profiles/r1_s7_shade): queue entries are read
+     * three iterations ahead, the record is prefetched two ahead, its primitive id read one ahead
+     * and that triangle's material index fetched at the end of the iteration before, so an
+     * iteration starts with every address it needs already in registers */
+    int32_t slot_next3 = (int64_t)qi + 2 * (int64_t)stride < n ? __ldcg(queue + qi + 2 * stride) : -1;
+    if (slot_next2 >= 0) prefetch_l2(pb.rec + slot_next2);
+    int32_t prim_next = slot_next >= 0 ? __ldcg(&pb.rec[slot_next].hit_prim) : -1;
+    int32_t mat_next = prim_next >= 0 ? __ldg(&S.shade[prim_next].material) : 0;
+#endif
     DeferredPush push_shadow, push_extend;
     push_shadow.init();
     push_extend.init();
@@ -450,8 +464,16 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
         uint32_t key_shadow = 0, key_extend = 0;
         const int32_t slot = slot_next;
         slot_next = slot_next2;
+#if PRT_SHADE_PIPE
+        const int32_t prim_cur = prim_next, mat_cur = mat_next;
+        slot_next2 = slot_next3;
+        slot_next3 = (int64_t)qi + 3 * (int64_t)stride < n ? __ldcg(queue + qi + 3 * stride) : -1;
+        if (slot_next2 >= 0) prefetch_l2(pb.rec + slot_next2);
+        prim_next = slot_next >= 0 ? __ldcg(&pb.rec[slot_next].hit_prim) : -1;
+#else
         slot_next2 = (int64_t)qi + 2 * (int64_t)stride < n ? __ldcg(queue + qi + 2 * stride) : -1;
-#if PRT_SHADE_PREFETCH
+#endif
+#if PRT_SHADE_PREFETCH && !PRT_SHADE_PIPE
         if (slot_next >= 0) {
             prefetch_l2(pb.rec + slot_next);
 #if PRT_SHADE_PREFETCH > 1
@@ -461,11 +483,17 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
 #endif
         if (slot >= 0) {
             PathRec* __restrict__ r = pb.rec + slot;
+#if PRT_SHADE_PIPE
+            const int32_t prim = prim_cur;
+            const TriShade* __restrict__ sh = S.shade + prim;
+            const DevMaterial m = S.materials[mat_cur];
+#else
             const int32_t prim = r->hit_prim;
-            const double t = r->hit[0], alpha = r->hit[1], beta = r->hit[2];
-            const d3 ro = ld3(r->o), rd = ld3(r->d);
             const TriShade* __restrict__ sh = S.shade + prim;
             const DevMaterial m = S.materials[sh->material];
+#endif
+            const double t = r->hit[0], alpha = r->hit[1], beta = r->hit[2];
+            const d3 ro = ld3(r->o), rd = ld3(r->d);
             /* the HitRecord of Triangle::Hit (Triangle.cpp:76-80,111) */
             Surface s;
             s.position = ro + rd * t;
@@ -526,6 +554,9 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
             }
             if (want_shadow && !want_extend) st3(r->o, s.position); /* shadow ray origin */
         }
+#if PRT_SHADE_PIPE
+        mat_next = prim_next >= 0 ? __ldg(&S.shade[prim_next].material) : 0;
+#endif
         __syncwarp();
         {
             int32_t* const q0[1] = {out_q[0]};

@@ -17,6 +17,18 @@ try:
 except Exception as e:
     print(n,'FAILED',e)
 PY
+  if [ -n "$AB_BATH" ]; then
+    PRT_B200_LIB=$lib timeout 300 python bench.py --scene bathroom2 --width 1280 --height 720 --depth 50 --steps 2 --no-cpu-baseline > gpurun_out/ab_bath_$n.json 2> gpurun_out/ab_bath_$n.err
+    python - "$n" <<'PY'
+import json,sys
+n=sys.argv[1]
+try:
+    j=json.loads(open(f'gpurun_out/ab_bath_{n}.json').read().strip().splitlines()[-1]); r=j['roofline']
+    print(f"   bathroom2   spp/s {j['value']:7.1f} Mrays/s {j['mrays_s']:7.0f} ms {j['ms_per_step']:6.2f} ext {r['extend_ms']:6.2f} shade {r['shade_ms']:6.2f} shadow {r['shadow_ms']:6.2f} chk {j['e2e']['image_checksum']:.9f}")
+except Exception as e:
+    print(n,'bath FAILED',e)
+PY
+  fi
   if [ $RQ = 1 ]; then
     PRT_B200_LIB=$lib timeout 300 python tools/rayquery_bench.py --tris 1 --rays 24 --mesh soup 2>/dev/null | python -c "
 import sys,json
