@@ -26,6 +26,7 @@ MAT_LAMBERTIAN, MAT_PHONG, MAT_MIRROR, MAT_COOK_TORRANCE, MAT_DIFFUSE_LIGHT, MAT
 ACCEL_REFERENCE_BVH2 = 0
 ACCEL_SAH_BVH2 = 1
 ACCEL_SAH_BVH4 = 2
+ACCEL_LBVH4_DEVICE = 3
 
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
@@ -122,6 +123,7 @@ class PrtStats(C.Structure):
         ("tri_bytes", C.c_int32),
         ("n_nodes", C.c_int64),
         ("n_triangles", C.c_int64),
+        ("build_ms", C.c_double),
     ]
 
 

@@ -244,9 +244,11 @@ class Scene:
         if accel is not None:
             self.commit(accel)
 
-    def commit(self, accel: int):
+    def commit(self, accel: int, max_leaf: int = 0):
+        """prt_scene_commit; max_leaf = triangles per leaf of the SAH / LBVH trees (0: the default, 4)"""
         o = capi.PrtBuildOpts()
         o.accel = int(accel)
+        o.reserved[0] = int(max_leaf)
         _check(self.lib, self.lib.prt_scene_commit(self.handle, C.byref(o)))
 
     def close(self):

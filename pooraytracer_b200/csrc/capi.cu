@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "../../include/prt_b200.h"
+#include "bvh_device.h"
 #include "launch.h"
 #include "scene_host.h"
 
@@ -99,6 +100,7 @@ struct prt_scene {
     DevBuf<uint8_t> d_prim_class;
     bool has_cook = false;
     int class_mask = 0;
+    float device_build_ms = 0.f; /* PRT_ACCEL_LBVH4_DEVICE: CUDA-event time of the build */
     DevScene dev;
 
     /* scratch for the host-pointer entry points */
@@ -319,11 +321,56 @@ void prt_scene_destroy(prt_scene* scene) {
 int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_scene_commit: null scene");
     const int accel = opts ? opts->accel : PRT_ACCEL_SAH_BVH2;
-    if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2 && accel != PRT_ACCEL_SAH_BVH4) return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
+    if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2 && accel != PRT_ACCEL_SAH_BVH4 && accel != PRT_ACCEL_LBVH4_DEVICE)
+        return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
     HostScene& h = s->host;
+    const bool dev_build = accel == PRT_ACCEL_LBVH4_DEVICE;
+    if (dev_build && s->ctx->device < 0)
+        return fail(PRT_ERR_NO_DEVICE, "prt_scene_commit: PRT_ACCEL_LBVH4_DEVICE builds on the GPU and this context has none (no CPU fallback)");
+    const int max_leaf = opts && opts->reserved[0] > 0 ? opts->reserved[0] : 4;
+    double scene_lo[3] = {0, 0, 0}, scene_hi[3] = {0, 0, 0}; /* bounding box of all triangles */
+    for (int64_t p = 0; p < h.n_tris; ++p)
+        for (int k = 0; k < 3; ++k) {
+            const double a = h.tri_box[p].v[2 * k], b = h.tri_box[p].v[2 * k + 1];
+            if (p == 0 || a < scene_lo[k]) scene_lo[k] = a;
+            if (p == 0 || b > scene_hi[k]) scene_hi[k] = b;
+        }
+    DeviceBvh dbvh;
     try {
-        int max_leaf = opts && opts->reserved[0] > 0 ? opts->reserved[0] : 4;
-        if (accel == PRT_ACCEL_SAH_BVH2) h.build_sah_bvh2(default_host_threads(), max_leaf);
+        if (dev_build) {
+            /* Morton sort, hierarchy, boxes, BVH4 emission and the triangle permutation
+             * all happen in HBM (bvh_device.cu); the host only learns the slot order, which the
+             * flattened reference tree's leaves refer to */
+            CUDA_TRY(cudaSetDevice(s->ctx->device));
+            cudaStream_t st = s->ctx->stream;
+            DevBuf<Box6> d_box;
+            DevBuf<TriIsect> d_isect;
+            CUDA_TRY(d_box.upload(h.tri_box, st));
+            CUDA_TRY(d_isect.upload(h.isect, st));
+            cudaError_t e = build_lbvh4_device(d_box.p, d_isect.p, h.n_tris, scene_lo, scene_hi, max_leaf, &dbvh, st);
+            if (e != cudaSuccess) {
+                cudaFree(dbvh.nodes4); cudaFree(dbvh.slot_prim); cudaFree(dbvh.tris);
+                return fail(e == cudaErrorMemoryAllocation ? PRT_ERR_OUT_OF_MEMORY : PRT_ERR_CUDA, std::string("device BVH build: ") + cudaGetErrorString(e));
+            }
+            h.nodes2.clear();
+            h.nodes4.clear();
+            h.isect_slots.clear();
+            h.sah_max_leaf = max_leaf;
+            h.slot_prim.assign((size_t)h.n_tris, 0);
+            h.prim_slot.assign((size_t)h.n_tris, -1);
+            if (h.n_tris > 0) {
+                e = cudaMemcpy(h.slot_prim.data(), dbvh.slot_prim, sizeof(int32_t) * (size_t)h.n_tris, cudaMemcpyDeviceToHost);
+                if (e != cudaSuccess) {
+                    cudaFree(dbvh.nodes4); cudaFree(dbvh.slot_prim); cudaFree(dbvh.tris);
+                    return fail(PRT_ERR_CUDA, std::string("device BVH build: ") + cudaGetErrorString(e));
+                }
+            }
+            for (int64_t sl = 0; sl < h.n_tris; ++sl) h.prim_slot[(size_t)h.slot_prim[(size_t)sl]] = (int32_t)sl;
+            s->d_nodes4.release(); s->d_slot_prim.release(); s->d_tris.release();
+            s->d_nodes4.p = dbvh.nodes4; s->d_nodes4.n = (size_t)dbvh.n_nodes4;
+            s->d_slot_prim.p = dbvh.slot_prim; s->d_slot_prim.n = (size_t)h.n_tris;
+            s->d_tris.p = dbvh.tris; s->d_tris.n = (size_t)h.n_tris;
+        } else if (accel == PRT_ACCEL_SAH_BVH2) h.build_sah_bvh2(default_host_threads(), max_leaf);
         else if (accel == PRT_ACCEL_SAH_BVH4) h.build_sah_bvh4(default_host_threads(), max_leaf);
         else h.use_reference_slots();
         h.flatten_reference_world();
@@ -331,23 +378,18 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
         return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_commit: out of host memory");
     }
     s->accel = accel;
-    s->stats.node_bytes = accel == PRT_ACCEL_SAH_BVH2 ? PRT_NODE2_BYTES : (accel == PRT_ACCEL_SAH_BVH4 ? PRT_NODE4_BYTES : PRT_REFNODE_BYTES);
+    const bool wide4 = accel == PRT_ACCEL_SAH_BVH4 || dev_build;
+    s->stats.node_bytes = accel == PRT_ACCEL_SAH_BVH2 ? PRT_NODE2_BYTES : (wide4 ? PRT_NODE4_BYTES : PRT_REFNODE_BYTES);
     s->stats.tri_bytes = PRT_TRI_BYTES;
-    s->stats.n_nodes = accel == PRT_ACCEL_SAH_BVH2 ? (int64_t)h.nodes2.size() : (accel == PRT_ACCEL_SAH_BVH4 ? (int64_t)h.nodes4.size() : (int64_t)h.ref_flat.size());
+    s->stats.n_nodes = accel == PRT_ACCEL_SAH_BVH2 ? (int64_t)h.nodes2.size()
+                                                   : (dev_build ? dbvh.n_nodes4 : (accel == PRT_ACCEL_SAH_BVH4 ? (int64_t)h.nodes4.size() : (int64_t)h.ref_flat.size()));
     s->stats.n_triangles = h.n_tris;
-    { /* ray-binning grid: PRT_KEY_GRID^3 cells over the bounding box of all triangles */
-        double lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
-        for (int64_t p = 0; p < h.n_tris; ++p)
-            for (int k = 0; k < 3; ++k) {
-                const double a = h.tri_box[p].v[2 * k], b = h.tri_box[p].v[2 * k + 1];
-                if (p == 0 || a < lo[k]) lo[k] = a;
-                if (p == 0 || b > hi[k]) hi[k] = b;
-            }
-        for (int k = 0; k < 3; ++k) {
-            const double ext = hi[k] - lo[k];
-            s->key_lo[k] = (float)lo[k];
-            s->key_scale[k] = ext > 0.0 && std::isfinite(ext) ? (float)(PRT_KEY_GRID / ext) : 0.f;
-        }
+    s->device_build_ms = dbvh.build_ms;
+    s->stats.build_ms = dbvh.build_ms;
+    for (int k = 0; k < 3; ++k) { /* ray-binning grid: PRT_KEY_GRID^3 cells over the scene's bounding box */
+        const double ext = scene_hi[k] - scene_lo[k];
+        s->key_lo[k] = (float)scene_lo[k];
+        s->key_scale[k] = ext > 0.0 && std::isfinite(ext) ? (float)(PRT_KEY_GRID / ext) : 0.f;
     }
     if (s->ctx->device < 0) { /* host-only context: flattening done, nothing to upload */
         s->committed = true;
@@ -373,11 +415,13 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
         if (c < CLS_SHADED) s->class_mask |= 1 << c;
     }
     std::vector<double> lut(h.srgb_lut, h.srgb_lut + 256);
-    CUDA_TRY(s->d_tris.upload(h.isect_slots, st));
-    CUDA_TRY(s->d_slot_prim.upload(h.slot_prim, st));
+    if (!dev_build) { /* the device build left these three in HBM already */
+        CUDA_TRY(s->d_tris.upload(h.isect_slots, st));
+        CUDA_TRY(s->d_slot_prim.upload(h.slot_prim, st));
+        CUDA_TRY(s->d_nodes4.upload(h.nodes4, st));
+    }
     CUDA_TRY(s->d_shade.upload(h.shade, st));
     CUDA_TRY(s->d_nodes2.upload(h.nodes2, st));
-    CUDA_TRY(s->d_nodes4.upload(h.nodes4, st));
     CUDA_TRY(s->d_ref_nodes.upload(h.ref_flat, st));
     CUDA_TRY(s->d_light_tris.upload(h.light_tris, st));
     CUDA_TRY(s->d_light_nodes.upload(h.light_nodes, st));
@@ -396,7 +440,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     D.slot_prim = s->d_slot_prim.p;
     D.shade = s->d_shade.p;
     D.nodes2 = accel == PRT_ACCEL_SAH_BVH2 && !h.nodes2.empty() ? s->d_nodes2.p : nullptr;
-    D.nodes4 = accel == PRT_ACCEL_SAH_BVH4 && !h.nodes4.empty() ? s->d_nodes4.p : nullptr;
+    D.nodes4 = (accel == PRT_ACCEL_SAH_BVH4 && !h.nodes4.empty()) || (dev_build && h.n_tris > 0) ? s->d_nodes4.p : nullptr;
     D.ref_nodes = s->d_ref_nodes.p;
     D.ref_root = h.ref_root_flat;
     D.n_nodes2 = (int32_t)h.nodes2.size();

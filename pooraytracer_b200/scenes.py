@@ -425,6 +425,25 @@ def soup(n=1_000_000, seed=1, size=None) -> SceneData:
     return b.build(cam)
 
 
+def few_triangles(n: int, seed=5) -> SceneData:
+    """n random triangles in the unit cube, one Lambertian mesh (degenerate sizes for the BVH builders)"""
+    b = _Builder(f"few-{n}")
+    mat = b.material(Material("DiffuseWhite", capi.MAT_LAMBERTIAN, kd=(0.7, 0.7, 0.7)))
+    c = hash_uniform(3 * n, seed, 0).reshape(n, 1, 3)
+    e = (hash_uniform(9 * n, seed, 1).reshape(n, 3, 3) - 0.5) * 0.8
+    b.mesh("few", mat, c + e)
+    return b.build(dict(width=64, height=64, fovy=40.0, eye=(0.5, 0.5, 3.0), look_at=(0.5, 0.5, 0.5), up=(0.0, 1.0, 0.0)))
+
+
+def repeated_triangle(n: int) -> SceneData:
+    """the same triangle n times: every box centre (hence every Morton code) equal, every hit an equal-t tie"""
+    b = _Builder(f"repeat-{n}")
+    mat = b.material(Material("DiffuseWhite", capi.MAT_LAMBERTIAN, kd=(0.7, 0.7, 0.7)))
+    tri = np.array([[[0.1, 0.1, 0.5], [0.9, 0.2, 0.4], [0.4, 0.9, 0.6]]])
+    b.mesh("repeat", mat, np.repeat(tri, n, axis=0))
+    return b.build(dict(width=64, height=64, fovy=40.0, eye=(0.5, 0.5, 3.0), look_at=(0.5, 0.5, 0.5), up=(0.0, 1.0, 0.0)))
+
+
 def random_rays(scene: SceneData, n: int, seed=2):
     """Origins uniform in the 1.5x-inflated bounding box, directions uniform on the sphere."""
     lo = scene.vertices.reshape(-1, 3).min(axis=0)

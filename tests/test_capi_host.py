@@ -31,7 +31,7 @@ def test_struct_sizes_match_header(built):
     assert C.sizeof(capi.PrtMaterial) == 8 + 8 * (3 + 3 + 1 + 3 + 2 + 3 + 3)
     assert C.sizeof(capi.PrtCamera) == 8 + 8 * 10
     assert C.sizeof(capi.PrtRenderParams) == 24 + 8 * 5
-    assert C.sizeof(capi.PrtStats) == 8 * 6 + 8 * 4 + 8 + 16
+    assert C.sizeof(capi.PrtStats) == 8 * 6 + 8 * 4 + 8 + 16 + 8
 
 
 @pytest.mark.parametrize("key", ["tiny", "cornell", "veach", "bathroom", "ties"])
@@ -70,6 +70,10 @@ def test_compute_calls_fail_loudly_without_gpu(built):
     assert e.value.code == capi.PRT_ERR_NO_DEVICE
     with pytest.raises(PrtError) as e:
         s.sample_lights(o, np.zeros((8, 4)))
+    assert e.value.code == capi.PRT_ERR_NO_DEVICE
+    # the GPU-built BVH has no host version either
+    with pytest.raises(PrtError) as e:
+        Scene(Context(-1), sc, accel=capi.ACCEL_LBVH4_DEVICE)
     assert e.value.code == capi.PRT_ERR_NO_DEVICE
 
 

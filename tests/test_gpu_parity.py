@@ -19,7 +19,7 @@ from pooraytracer_b200 import Scene, _capi as capi, make_camera, make_params, sc
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-ACCELS = [capi.ACCEL_SAH_BVH2, capi.ACCEL_SAH_BVH4, capi.ACCEL_REFERENCE_BVH2]
+ACCELS = [capi.ACCEL_SAH_BVH2, capi.ACCEL_SAH_BVH4, capi.ACCEL_REFERENCE_BVH2, capi.ACCEL_LBVH4_DEVICE]
 
 
 def gold(name):
@@ -85,6 +85,39 @@ def test_soup_vs_oracle(gpu_ctx):
     s = Scene(gpu_ctx, sc)
     got = s.trace_closest(o, d, 1e-4, np.inf)
     for x, y in zip(got, want):
+        assert np.array_equal(x, y)
+
+
+def test_device_built_bvh(gpu_ctx):
+    """PRT_ACCEL_LBVH4_DEVICE: the GPU-built tree returns the oracle's hits on a soup (no
+    spatial order in the input, many equal Morton prefixes), for every leaf size, on degenerate inputs
+    (all triangles identical: every Morton code equal; 1, 2 and 5 triangles), and reports its build time."""
+    sc = scenes.soup(50_000)
+    o, d = scenes.random_rays(sc, 100_000)
+    O = ol.OracleScene("orc", sc, 0)
+    want = O.trace_closest(o, d, 1e-4, np.inf, nthreads=os.cpu_count() or 4)
+    for max_leaf in (1, 4, 8):
+        s = Scene(gpu_ctx, sc, accel=None)
+        s.commit(capi.ACCEL_LBVH4_DEVICE, max_leaf=max_leaf)
+        st = s.stats()
+        assert st.build_ms > 0 and st.n_nodes > 0 and st.node_bytes == 128
+        got = s.trace_closest(o, d, 1e-4, np.inf)
+        for x, y in zip(got, want):
+            assert np.array_equal(x, y)
+        tmax = np.full(len(o), 0.7)
+        assert np.array_equal(s.trace_any(o, d, 1e-3, tmax).astype(bool), O.trace_closest(o, d, 1e-3, tmax, nthreads=os.cpu_count() or 4)[0] >= 0)
+    for n_keep in (1, 2, 5):
+        sub = scenes.few_triangles(n_keep)
+        O2 = ol.OracleScene("orc", sub, 0)
+        o2, d2 = scenes.random_rays(sub, 4096)
+        s2 = Scene(gpu_ctx, sub, accel=capi.ACCEL_LBVH4_DEVICE)
+        for x, y in zip(s2.trace_closest(o2, d2, 1e-4, np.inf), O2.trace_closest(o2, d2, 1e-4, np.inf)):
+            assert np.array_equal(x, y)
+    same = scenes.repeated_triangle(300)
+    O3 = ol.OracleScene("orc", same, 0)
+    o3, d3 = scenes.random_rays(same, 4096)
+    s3 = Scene(gpu_ctx, same, accel=capi.ACCEL_LBVH4_DEVICE)
+    for x, y in zip(s3.trace_closest(o3, d3, 1e-4, np.inf), O3.trace_closest(o3, d3, 1e-4, np.inf)):
         assert np.array_equal(x, y)
 
 
