@@ -431,8 +431,8 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     CUDA_TRY(s->d_srgb.upload(lut, st));
     CUDA_TRY(s->d_prim_class.upload(prim_class, st));
     CUDA_TRY(s->d_fetch.ensure(4));
-    CUDA_TRY(s->d_counters.ensure(4));
-    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(s->d_counters.ensure(8));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 8 * sizeof(unsigned long long), st));
     if (int e = ensure_sort_scratch(s, st)) return e;
     CUDA_TRY(cudaStreamSynchronize(st));
     DevScene& D = s->dev;
@@ -482,7 +482,7 @@ int prt_set_counters(prt_scene* s, int enable) {
 static int trace_begin(prt_scene* s, int64_t n, cudaStream_t st) {
     if (n < 0 || n >= (int64_t(1) << 31) - 64) return fail(PRT_ERR_INVALID_ARGUMENT, "ray count out of range");
     CUDA_TRY(cudaMemsetAsync(s->d_fetch.p, 0, 4 * sizeof(int32_t), st));
-    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 8 * sizeof(unsigned long long), st));
     CUDA_TRY(cudaEventRecord(s->ev0, st));
     return PRT_OK;
 }
@@ -649,7 +649,7 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     rc = ensure_pool(s, (int64_t)per_pass * rcn.npix, n_bounces);
     if (rc) return rc;
     const bool counting = (rcn.flags & PRT_RENDER_COUNTERS) != 0;
-    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 8 * sizeof(unsigned long long), st));
     PathBuffers pb = path_buffers(s);
     pb.counters = counting ? s->d_counters.p : nullptr;
     LaunchConfig lc = launch_config(s->ctx);
@@ -759,8 +759,10 @@ int prt_get_stats(const prt_scene* cs, prt_stats* out) {
             s->timing_pending = false;
         }
         if (s->rays_pending || s->visits_pending) {
-            unsigned long long c[4] = {0, 0, 0, 0};
+            unsigned long long c[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             if (cudaMemcpy(c, s->d_counters.p, sizeof(c), cudaMemcpyDeviceToHost) == cudaSuccess) {
+                if (s->visits_pending && std::getenv("PRT_DEBUG_RECHECK"))
+                    std::fprintf(stderr, "[prt] reference re-trace: %llu rays, %llu fetches, most for one ray %llu (all fetches: %llu)\n", c[4], c[5], c[6], c[0] + c[1]);
                 if (s->visits_pending) { s->stats.node_visits = c[0]; s->stats.tri_tests = c[1]; }
                 if (s->rays_pending) { s->stats.extend_rays = c[2]; s->stats.shadow_rays = c[3]; }
             }

@@ -80,6 +80,11 @@ __device__ __forceinline__ void flush_counters(const VisitCounters& c, unsigned 
         atomicAdd(out, n);
         atomicAdd(out + 1, t);
     }
+    if (c.rechecks) { /* rare: out[4..6] = re-traced rays, their fetches, the most one ray fetched */
+        atomicAdd(out + 4, c.rechecks);
+        atomicAdd(out + 5, c.recheck_visits);
+        atomicMax(out + 6, c.recheck_max);
+    }
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -224,7 +229,7 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(
                                                        const double* __restrict__ tmin, const double* __restrict__ tmax,
                                                        int32_t* __restrict__ prim, double* __restrict__ t, double* __restrict__ alpha,
                                                        double* __restrict__ beta, const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
-    VisitCounters cnt = {0, 0};
+    VisitCounters cnt = {0, 0, 0, 0, 0};
     ClosestQueryPolicy pol = {o, d, tmin, tmax, prim, t, alpha, beta, S.slot_prim, order};
     traverse_persistent<false, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
@@ -234,7 +239,7 @@ template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                    const double* __restrict__ tmin, const double* __restrict__ tmax, uint8_t* __restrict__ hit,
                                                    const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
-    VisitCounters cnt = {0, 0};
+    VisitCounters cnt = {0, 0, 0, 0, 0};
     AnyQueryPolicy pol = {o, d, tmin, tmax, hit, order};
     traverse_persistent<true, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
     flush_counters<COUNT>(cnt, counters);
@@ -411,7 +416,7 @@ __device__ __forceinline__ void extend_body(const DevScene& S, const uint8_t* __
 
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
-    VisitCounters cnt = {0, 0};
+    VisitCounters cnt = {0, 0, 0, 0, 0};
     extend_body<COUNT, WIDE>(S, prim_class, rc, pb, bounce, sorted, cnt);
     flush_counters<COUNT>(cnt, pb.counters);
 }
@@ -657,7 +662,7 @@ __device__ __forceinline__ void shadow_body(const DevScene& S, const RenderConst
 
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
-    VisitCounters cnt = {0, 0};
+    VisitCounters cnt = {0, 0, 0, 0, 0};
     shadow_body<COUNT, WIDE>(S, rc, pb, bounce, sorted, cnt);
     flush_counters<COUNT>(cnt, pb.counters);
 }
@@ -673,7 +678,7 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScen
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, 2) k_tail(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int first) {
     cg::grid_group grid = cg::this_grid();
-    VisitCounters cnt = {0, 0};
+    VisitCounters cnt = {0, 0, 0, 0, 0};
     for (int b = first; b <= rc.max_depth; ++b) {
         if (b > 0 && __ldcg(&pb.ctrl[b].n_extend) == 0) break; /* uniform: written before the last barrier */
         extend_body<COUNT, WIDE>(S, prim_class, rc, pb, b, 0, cnt);

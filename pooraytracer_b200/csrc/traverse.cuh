@@ -34,6 +34,9 @@ struct Hit {
  * (PRT_RENDER_COUNTERS / prt_set_counters), which feed the roofline's algorithmic bytes */
 struct VisitCounters {
     unsigned long long nodes, tris;
+    /* diagnostics of the reference-order re-trace (boundary / equal-t hits): how many rays took it, the
+     * nodes + triangles they fetched there, the most one ray fetched */
+    unsigned long long rechecks, recheck_visits, recheck_max;
 };
 #define PRT_COUNT_NODE(c) do { if (COUNT) (c).nodes++; } while (0)
 #define PRT_COUNT_TRI(c) do { if (COUNT) (c).tris++; } while (0)

@@ -47,10 +47,27 @@ namespace prt {
 #define PRT_REFILL_BELOW 16      /* refill idle lanes once fewer than this many lanes hold a ray */
 #endif
 
+/* PRT_BOX_AXIS_ERR = 1 (default): the origin error of each axis is folded into that axis alone.
+ * The first version padded the final entry / exit distances with the LARGEST of the three axis
+ * errors. A scattered ray with one direction component of ~1e-8 (a cosine-hemisphere sample at the
+ * rim of the disk, leaving a wall tangentially) has |o| |1/d| 2^-22 ~ 5 on that axis: the pad then
+ * exceeded the length of the ray, no box was ever culled by the closest hit so far, and ONE such ray
+ * walked 88 000 nodes of the displaced wall it grazed — a serial chain that held its launch for
+ * 100 ms (profiles/r1_s13_grazing_rays.txt). With per-axis errors the two well-conditioned axes
+ * keep their tight bounds and cull as usual. */
+#ifndef PRT_BOX_AXIS_ERR
+#define PRT_BOX_AXIS_ERR 1
+#endif
+
 struct RayF32 { /* the FP32 side of a ray, for box tests only: t = b * inv - o * inv */
     float ix, iy, iz;    /* fl32(1 / d), clamped */
+#if PRT_BOX_AXIS_ERR
+    float nx, ny, nz;    /* o32 * inv32 + err(axis), rounded up: subtracted from the NEAR plane's product */
+    float fx, fy, fz;    /* o32 * inv32 - err(axis), rounded down: subtracted from the FAR plane's product */
+#else
     float ox, oy, oz;    /* fl32(o32 * inv32) */
     float err;           /* max over the axes of |o32| |inv32| 2^-22 (rounded up) */
+#endif
 };
 
 __device__ __forceinline__ float clamp_inv(double d) {
@@ -62,19 +79,41 @@ __device__ __forceinline__ RayF32 make_ray_f32(d3 o, d3 d) {
     RayF32 r;
     const float ox = (float)o.x, oy = (float)o.y, oz = (float)o.z;
     r.ix = clamp_inv(d.x); r.iy = clamp_inv(d.y); r.iz = clamp_inv(d.z);
+    const float ex = __fmul_ru(__fmul_ru(fabsf(ox), fabsf(r.ix)), 2.3841858e-7f); /* |o32| |inv32| 2^-22 */
+    const float ey = __fmul_ru(__fmul_ru(fabsf(oy), fabsf(r.iy)), 2.3841858e-7f);
+    const float ez = __fmul_ru(__fmul_ru(fabsf(oz), fabsf(r.iz)), 2.3841858e-7f);
+#if PRT_BOX_AXIS_ERR
+    const float px = ox * r.ix, py = oy * r.iy, pz = oz * r.iz;
+    r.nx = __fadd_ru(px, ex); r.ny = __fadd_ru(py, ey); r.nz = __fadd_ru(pz, ez);
+    r.fx = __fadd_rd(px, -ex); r.fy = __fadd_rd(py, -ey); r.fz = __fadd_rd(pz, -ez);
+#else
     r.ox = ox * r.ix; r.oy = oy * r.iy; r.oz = oz * r.iz;
-    const float ex = __fmul_ru(fabsf(ox), fabsf(r.ix)), ey = __fmul_ru(fabsf(oy), fabsf(r.iy)), ez = __fmul_ru(fabsf(oz), fabsf(r.iz));
-    r.err = __fmul_ru(fmaxf(ex, fmaxf(ey, ez)), 2.3841858e-7f); /* 2^-22 */
+    r.err = fmaxf(ex, fmaxf(ey, ez));
+#endif
     return r;
 }
 
 /* Padded FP32 slab test. Per axis t = fma(b, inv32, -o32 * inv32); with E = the largest computed near
  * value and X = the smallest computed far value, the exact entry distance is >= the exact near value
- * of E's axis >= E - |E| eps - err, and the exact exit distance <= X + |X| eps + err, so padding the
- * two extremes once is as safe as padding all six values. fmaxf / fminf drop NaNs (inf - inf of an
- * overflowed bound): such an axis does not constrain. */
+ * of E's axis >= E - |E| eps - err(axis), and the exact exit distance <= X + |X| eps + err(axis), so
+ * padding the two extremes once by the relative term is as safe as padding all six values; the
+ * absolute term err(axis) rides in the biased origin products (nx / fx ...), whose > 2x margin over
+ * the real origin error (2^-23 |o| |inv|) also absorbs the relative error of a near value that the
+ * bias has pulled towards zero. The near plane of an axis is picked by the sign of inv32 (lo <= hi
+ * for real boxes; an unused child holds lo = +inf, hi = -inf and fails either way). fmaxf / fminf
+ * drop NaNs (inf - inf of an overflowed bound, 0 * inf): such an axis does not constrain. */
 __device__ __forceinline__ bool box_f32(float lx, float ly, float lz, float hx, float hy, float hz, const RayF32& r, float tmin32,
                                         float tbest32, float& entry) {
+#if PRT_BOX_AXIS_ERR
+    const bool sx = r.ix < 0.f, sy = r.iy < 0.f, sz = r.iz < 0.f;
+    const float ax = fmaf(sx ? hx : lx, r.ix, -r.nx), bx = fmaf(sx ? lx : hx, r.ix, -r.fx);
+    const float ay = fmaf(sy ? hy : ly, r.iy, -r.ny), by = fmaf(sy ? ly : hy, r.iy, -r.fy);
+    const float az = fmaf(sz ? hz : lz, r.iz, -r.nz), bz = fmaf(sz ? lz : hz, r.iz, -r.fz);
+    const float E = fmaxf(fmaxf(ax, ay), az);
+    const float X = fminf(fminf(bx, by), bz);
+    entry = fmaxf(fmaf(-PRT_BOX_EPS, fabsf(E), E), tmin32);
+    const float exit = fminf(fmaf(PRT_BOX_EPS, fabsf(X), X), tbest32);
+#else
     const float ax = fmaf(lx, r.ix, -r.ox), bx = fmaf(hx, r.ix, -r.ox);
     const float ay = fmaf(ly, r.iy, -r.oy), by = fmaf(hy, r.iy, -r.oy);
     const float az = fmaf(lz, r.iz, -r.oz), bz = fmaf(hz, r.iz, -r.oz);
@@ -82,6 +121,7 @@ __device__ __forceinline__ bool box_f32(float lx, float ly, float lz, float hx, 
     const float X = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
     entry = fmaxf(fmaf(-PRT_BOX_EPS, fabsf(E), E) - r.err, tmin32);
     const float exit = fminf(fmaf(PRT_BOX_EPS, fabsf(X), X) + r.err, tbest32);
+#endif
     return entry <= exit;
 }
 
@@ -136,6 +176,9 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     int32_t cur = PRT_DONE;
     int32_t leaf = -1; /* PRT_WALK_MODE 1: parked leaf, (slot << 3) | (triangles left - 1) */
     int32_t slot = -1;
+#ifdef PRT_DEBUG_SLOW_RAY
+    unsigned long long dbg_start = 0;
+#endif
     bool has_ray = false, exhausted = false, recheck = false;
     d3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
     double tmin = 0.0, tmax = 0.0, tbest = 0.0;
@@ -158,8 +201,25 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     for (;;) {
         /* ---- retire finished lanes, refill idle ones ---- */
         const bool finished = has_ray && cur == PRT_DONE && leaf < 0;
+#ifdef PRT_DEBUG_SLOW_RAY
+        if (COUNT && finished) {
+            const unsigned long long v = cnt.nodes + cnt.tris - dbg_start;
+            if (v > 20000ull)
+                printf("[slow ray] fetches %llu slot %d o %.17g %.17g %.17g d %.17g %.17g %.17g tmin %g tmax %g hit %d t %.17g any %d\n", v, slot, o.x, o.y, o.z,
+                       d.x, d.y, d.z, tmin, tmax, hit.slot, hit.t, (int)ANY);
+        }
+#endif
         if (finished) {
-            if (recheck) trace_reference_cold<ANY, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+            if (recheck) {
+                const unsigned long long before = cnt.nodes + cnt.tris;
+                trace_reference_cold<ANY, COUNT>(S, o, d, tmin, tmax, hit, cnt);
+                if (COUNT) {
+                    const unsigned long long v = cnt.nodes + cnt.tris - before;
+                    cnt.rechecks++;
+                    cnt.recheck_visits += v;
+                    if (v > cnt.recheck_max) cnt.recheck_max = v;
+                }
+            }
             has_ray = false;
         }
         __syncwarp();
@@ -198,12 +258,25 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
             if (mine >= 0) {
                 slot = mine;
                 if (pol.load(slot, o, d, tmin, tmax)) {
+#ifdef PRT_DEBUG_SLOW_RAY
+                    dbg_start = cnt.nodes + cnt.tris;
+#endif
                     has_ray = true;
                     recheck = false;
                     hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
                     tbest = tmax;
                     sp = 0;
-                    if (use_sah) {
+                    /* A ray with a NaN coordinate (a scattered direction of 0/0: the reference scrubs
+                     * such pixels at the very end, Camera.cpp:291-293) misses every triangle: n.o or n.d
+                     * is NaN, t is NaN, Interval::Contains is false (Triangle.cpp:56-62) — likewise a
+                     * NaN upper bound. But its box tests never fail either (AABB.cpp:38-64: every
+                     * comparison with NaN is false, nothing shrinks), so it would walk the WHOLE tree,
+                     * 1.6 M dependent fetches on the 1 M-triangle room: one such ray held a launch for
+                     * ~50 ms (profiles/r1_s13_nan_rays.txt). The miss is known up front. */
+                    const bool poisoned = o.x != o.x || o.y != o.y || o.z != o.z || d.x != d.x || d.y != d.y || d.z != d.z || tmax != tmax;
+                    if (poisoned) {
+                        cur = PRT_DONE;
+                    } else if (use_sah) {
                         rf = make_ray_f32(o, d);
                         tmin32 = __double2float_rd(tmin);
                         tbest32 = __double2float_ru(tbest);

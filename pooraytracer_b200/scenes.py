@@ -382,6 +382,11 @@ def tiny_scene(kind="mixed") -> SceneData:
                                      eta=(0.3, 0.7, 1.1), k=(4.4, 3.1, 2.5)))
         box_m = b.material(Material("CookAlumina", capi.MAT_COOK_TORRANCE, kd=(0.9, 0.9, 0.9), alpha_x=0.6, alpha_y=0.05,
                                     eta=(1.75, 1.76, 1.78), k=(0.0, 0.0, 0.0)))
+    if kind == "debug":
+        # DebugMaterial (Source/Material.h:523-535, Model.cpp:317-319): HasEmission() is true and it
+        # emits its albedo, so main.cpp:40 also lists its meshes among the lights
+        ball_m = b.material(Material("DebugBall", capi.MAT_DEBUG, kd=(0.9, 0.3, 0.1)))
+        box_m = b.material(Material("DebugBox", capi.MAT_DEBUG, kd=(0.1, 0.5, 1.5)))
     b.mesh("floor", texm, *grid((-1, 0, 1), (2, 0, 0), (0, 0, -2), 3, 3))
     b.mesh("ceiling", white, *quad((-1, 2, -1), (1, 2, -1), (1, 2, 1), (-1, 2, 1)))
     b.mesh("backWall", ph_d, *quad((-1, 0, -1), (1, 0, -1), (1, 2, -1), (-1, 2, -1)))

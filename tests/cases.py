@@ -29,6 +29,10 @@ def cook():
     return scenes.tiny_scene("cook")
 
 
+def debug():
+    return scenes.tiny_scene("debug")
+
+
 SCENES = {"tiny": tiny, "cornell": cornell_small, "veach": veach_small, "bathroom": bathroom_small}
 
 
@@ -128,7 +132,7 @@ def eval_inputs(n=64, seed=8):
 
 
 # scenes that only the render / material fixtures use (no ray fixtures)
-EXTRA_SCENES = {"cook": cook}
+EXTRA_SCENES = {"cook": cook, "debug": debug}
 
 RENDER_CASES = {
     # name: (scene key, width, height, spp, depth, sample_lights, rng_key, background)
@@ -139,6 +143,8 @@ RENDER_CASES = {
     "bathroom_nee": ("bathroom", 48, 27, 2, 12, True, 7, (0.0, 0.0, 0.0)),
     "cook_nee": ("cook", 48, 32, 4, 8, True, 13, (0.0, 0.0, 0.0)),
     "cook_plain": ("cook", 24, 16, 3, 6, False, 17, (0.2, 0.3, 0.1)),
+    "debug_nee": ("debug", 48, 32, 4, 8, True, 19, (0.0, 0.0, 0.0)),
+    "debug_plain": ("debug", 24, 16, 3, 6, False, 23, (0.05, 0.05, 0.1)),
 }
 
 

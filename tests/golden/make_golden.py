@@ -63,6 +63,10 @@ def main():
     assert ol.available("ref"), "build oracle/_ref first (make -C oracle ref)"
     if len(sys.argv) > 1 and sys.argv[1] == "cook":
         return cook_fixtures()
+    if len(sys.argv) > 1 and sys.argv[1] == "debug":  # DebugMaterial renders only
+        for name in ("debug_nee", "debug_plain"):
+            render_fixture(name)
+        return
     tag = ol.PER_TRIANGLE_MATERIAL | ol.UV_TAG
     for key, make in list(cases.SCENES.items()) + [("ties", cases.tie_scene)]:
         sc = make()

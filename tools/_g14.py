@@ -1,0 +1,16 @@
+import sys, os
+sys.path.insert(0, '.')
+import torch
+from pooraytracer_b200 import Context, Scene, _capi as capi, scenes, make_camera, make_params
+ctx = Context(0)
+sc = scenes.bathroom_like()
+s = Scene(ctx, sc, accel=capi.ACCEL_SAH_BVH4)
+s.set_counters(True)
+cam = make_camera(sc.camera, 1280, 720)
+acc = torch.zeros(1280 * 720 * 3, dtype=torch.float64, device="cuda")
+st = torch.cuda.Stream()
+for step in (3, 9):
+    prm = make_params(3000, 50, rr=0.8, rng_key=20251104, spp_begin=step * 16, spp_end=(step + 1) * 16)
+    s.render_device(cam, prm, acc.data_ptr(), st.cuda_stream)
+    x = s.stats()
+    print("step", step, "gpu_ms", round(x.gpu_ms, 2), flush=True)
