@@ -282,6 +282,21 @@ def run_b200(a):
     e2e_value = e2e_steps * S * world / float(e2e_t.item())
     checksum = float(host_img.sum().item())
 
+    # DRAM traffic of the traversal kernels over one step, from the committed ncu pass of this very
+    # workload (profiles/r1_traffic.json; a profiler cannot run inside a timed bench): same basis as
+    # `achieved`, which is the step's algorithmic bytes over the step's traversal time
+    traffic = traffic_note = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        if (tj["workload"] == a.scene and tj["accel"] == a.accel and tj["spp_per_step"] == S and a.width == WIDTH and a.height == HEIGHT
+                and a.depth == DEPTH):
+            traffic = tj["traversal_dram_bytes_per_step"]
+            traffic_note = (f"dram read+write of k_extend + k_shadow summed over the {tj['traversal_launches_per_step']:.0f} launches of one step "
+                            f"(ncu, profiles/r1_traffic.json); algorithmic bytes of the same step: {bytes_per_ray * stage_rays / max(1, n_stage):.4g} "
+                            "(cache-oblivious: the 2.5 MB scene is L1/L2-resident, DRAM carries the path records)")
+    except Exception:
+        pass
+
     if rank == 0:
         line = {
             "metric": "spp_per_s", "value": value, "unit": "spp/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -298,7 +313,7 @@ def run_b200(a):
             "e2e": {"value": e2e_value, "unit": "spp/s", "h2d_bytes_per_step": C.sizeof(cam) + C.sizeof(params(0)),
                     "d2h_bytes_per_step": npix * 3 * 8, "steps": e2e_steps, "image_checksum": checksum},
             "gpu_launches": int(tot[1].item()),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "kernel": "k_extend + k_shadow (BVH traversal)", "bytes_per_ray": bytes_per_ray,
                          "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "node_bytes": st.node_bytes, "tri_bytes": st.tri_bytes,

@@ -204,7 +204,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
 #ifdef PRT_DEBUG_SLOW_RAY
         if (COUNT && finished) {
             const unsigned long long v = cnt.nodes + cnt.tris - dbg_start;
-            if (v > 20000ull)
+            if (v > PRT_DEBUG_SLOW_RAY)
                 printf("[slow ray] fetches %llu slot %d o %.17g %.17g %.17g d %.17g %.17g %.17g tmin %g tmax %g hit %d t %.17g any %d\n", v, slot, o.x, o.y, o.z,
                        d.x, d.y, d.z, tmin, tmax, hit.slot, hit.t, (int)ANY);
         }
