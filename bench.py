@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4", "lbvh"])
     ap.add_argument("--cpu-spp", type=int, default=1, help="spp of the bounded CPU sample")
+    ap.add_argument("--max-leaf", type=int, default=0, help="triangles per BVH leaf (0 = the library's default, 4)")
     return ap.parse_args()
 
 
@@ -188,7 +189,7 @@ def run_b200(a):
     scene = Scene(ctx, sc, accel=None)
     t_create = time.time() - t0
     t0 = time.time()
-    scene.commit({"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE}[a.accel])
+    scene.commit({"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE}[a.accel], max_leaf=a.max_leaf)
     t_commit = time.time() - t0
     cam = make_camera(sc.camera, a.width, a.height)
     npix = a.width * a.height

@@ -135,6 +135,11 @@ typedef struct prt_camera {
 #define PRT_RENDER_EXACT_VISIBILITY 1u /* NEE visibility by closest-hit + the literal distance test
                                           of Source/Camera.cpp:150-155 instead of any-hit over
                                           [1e-3, dist-1e-3] (equivalent up to rounding)          */
+#define PRT_RENDER_PIXEL_JITTER 8u     /* OFF by default and never part of parity with the shipped
+                                          reference: the sample position Camera::GetRay's commented-out
+                                          lines intend (Source/Camera.cpp:110-111, SampleSquare(),
+                                          RandomNumberGenerator.h:65-68): pixel + (u0 - .5, u1 - .5),
+                                          drawn as the first two numbers of the sample's stream    */
 #define PRT_RENDER_COUNTERS 2u         /* count BVH node / triangle visits (prt_get_stats)       */
 #define PRT_RENDER_STAGE_TIMING 4u     /* CUDA events around the extend / shade / shadow kernels of
                                           every bounce (prt_stats.extend_ms ...); the call then

@@ -689,6 +689,15 @@ struct Cam {
         o = center;
         d = ps - o;
     }
+    // PRT_RENDER_PIXEL_JITTER: the commented-out lines Camera.cpp:110-111 with SampleSquare()
+    // (RandomNumberGenerator.h:65-68); NOT what the shipped reference renders
+    void GetRayJittered(int i, int j, Rng& rng, V3& o, V3& d) const {
+        const double ox = rng.RandomDouble() - 0.5;
+        const double oy = rng.RandomDouble() - 0.5;
+        V3 ps = pixel00 + ((double)i + ox) * dU + ((double)j + oy) * dV;
+        o = center;
+        d = ps - o;
+    }
 };
 
 struct Counters { uint64_t hits = 0, shadows = 0; };
@@ -939,6 +948,7 @@ int orc_render(void* p, const prt_camera* c, const prt_render_params* prm, int r
                 for (int smp = sb; smp < se; ++smp) {  // Camera.cpp:54-57
                     rng.seed = orc_stream_seed(prm->rng_key, pix, (uint32_t)smp);
                     rng.dim = 0;
+                    if (prm->flags & PRT_RENDER_PIXEL_JITTER) cam.GetRayJittered(i, (int)j, rng, ro, rd);
                     acc = acc + I.RayColor(ro, rd, prm->max_depth, rng) * scale;
                 }
                 rgb[3 * (size_t)pix] = acc.x; rgb[3 * (size_t)pix + 1] = acc.y; rgb[3 * (size_t)pix + 2] = acc.z;
@@ -974,6 +984,7 @@ int orc_pixel_samples(void* p, const prt_camera* c, const prt_render_params* prm
     for (int smp = sb; smp < se; ++smp) {
         rng.seed = orc_stream_seed(prm->rng_key, pix, (uint32_t)smp);
         rng.dim = 0;
+        if (prm->flags & PRT_RENDER_PIXEL_JITTER) cam.GetRayJittered(px, py, rng, ro, rd);
         V3 L = I.RayColor(ro, rd, prm->max_depth, rng);
         out[3 * (smp - sb)] = L.x; out[3 * (smp - sb) + 1] = L.y; out[3 * (smp - sb) + 2] = L.z;
     }

@@ -31,6 +31,7 @@ ACCEL_LBVH4_DEVICE = 3
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
 RENDER_STAGE_TIMING = 4
+RENDER_PIXEL_JITTER = 8
 
 LOAD_STRTOD = 1
 

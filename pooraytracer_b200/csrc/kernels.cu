@@ -271,7 +271,16 @@ __device__ __forceinline__ void st3(double* p, d3 v) {
 __device__ __forceinline__ void camera_ray(const RenderConst& rc, int32_t slot, d3& o, d3& d) {
     const int pix = slot % rc.npix;
     const int i = pix % rc.width, j = pix / rc.width;
-    const d3 ps = rc.pixel00 + ((double)i) * rc.dU + ((double)j) * rc.dV;
+    double fi = (double)i, fj = (double)j;
+    if (rc.flags & PRT_RENDER_PIXEL_JITTER) {
+        /* the commented-out lines of Camera.cpp:110-111: + SampleSquare(), the first two draws of the stream */
+        Rng rng;
+        rng.seed = stream_seed(rc.rng_key, (uint32_t)pix, (uint32_t)(rc.sample_first + slot / rc.npix));
+        rng.dim = 0u;
+        fi = fi + (rng.next() - 0.5);
+        fj = fj + (rng.next() - 0.5);
+    }
+    const d3 ps = rc.pixel00 + fi * rc.dU + fj * rc.dV;
     o = rc.center;
     d = ps - rc.center;
 }
@@ -387,7 +396,7 @@ struct ExtendPolicy {
                         st3(r->o, o);
                         st3(r->d, d);
                         st3(r->T, mk3(1.0, 1.0, 1.0));
-                        r->dim = 0u;
+                        r->dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u;
                         r->flags = 0u;
                     }
                     cls = c;

@@ -446,7 +446,7 @@ struct SahBuilder {
     std::atomic<int32_t>& next;
     int max_leaf;
     static constexpr int NB = 16;
-    static constexpr double C_TRI = 1.25, C_NODE = 1.0;
+    double C_TRI = 1.25, C_NODE = 1.0; /* PRT_SAH_CTRI overrides C_TRI (experiments) */
 
     int32_t alloc() { return next.fetch_add(1); }
 
@@ -559,6 +559,7 @@ static void build_sah_tree(HostScene& s, int n_threads, int max_leaf, std::vecto
     int par = 0;
     while ((1 << par) < n_threads) ++par;
     SahBuilder b{s, idx, tmp, next, max_leaf};
+    if (const char* e = std::getenv("PRT_SAH_CTRI")) b.C_TRI = std::atof(e);
     b.build(0, 0, (int32_t)s.n_tris, par + 1);
 }
 

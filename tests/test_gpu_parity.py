@@ -266,6 +266,27 @@ def test_ray_binning_changes_nothing(gpu_ctx, accel, monkeypatch):
     assert np.array_equal(p_on, s.trace_closest(o2, d, 1e-4, np.inf)[0])
 
 
+def test_pixel_jitter_opt_in(gpu_ctx):
+    """PRT_RENDER_PIXEL_JITTER (SURVEY 8 f4, default OFF): the sample position Camera::GetRay's commented-out
+    lines intend. The shipped reference cannot render it, so parity here is CUDA against the oracle port
+    (same bar as the golden renders; what jitter means for the image is tested on the port, CPU suite)."""
+    sc, cam, prm = _render_case("tiny_nee")
+    s = Scene(gpu_ctx, sc)
+    O = ol.OracleScene("orc", sc, ol.DEFINE_UB)
+    base = s.render(cam, prm)
+    pj = make_params(prm.samples_per_pixel, prm.max_depth, rng_key=prm.rng_key, flags=capi.RENDER_PIXEL_JITTER)
+    img = s.render(cam, pj)
+    ref, _ = O.render(cam, pj)
+    _compare_images(img, ref, "tiny_nee jittered vs port")
+    assert not np.array_equal(img, base)
+    # per-bounce launches and the tail kernel agree under jitter too (the RNG dimension starts at 2)
+    os.environ["PRT_TAIL_PATHS"] = "0"
+    try:
+        assert np.array_equal(s.render(cam, pj), img)
+    finally:
+        del os.environ["PRT_TAIL_PATHS"]
+
+
 def test_resolve_matches_reference_quantiser(gpu_ctx):
     import torch
     sc, cam, prm = _render_case("tiny_nee")
