@@ -57,7 +57,7 @@ def parse():
     ap.add_argument("--depth", type=int, default=DEPTH)
     ap.add_argument("--scene", default="cornell-box", choices=["cornell-box", "veach-mis", "bathroom2"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4", "lbvh"])
+    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4", "lbvh", "bvh4q"])
     ap.add_argument("--cpu-spp", type=int, default=1, help="spp of the bounded CPU sample")
     ap.add_argument("--max-leaf", type=int, default=0, help="triangles per BVH leaf (0 = the library's default, 4)")
     return ap.parse_args()
@@ -189,7 +189,7 @@ def run_b200(a):
     scene = Scene(ctx, sc, accel=None)
     t_create = time.time() - t0
     t0 = time.time()
-    scene.commit({"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE}[a.accel], max_leaf=a.max_leaf)
+    scene.commit({"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE, "bvh4q": capi.ACCEL_SAH_BVH4Q}[a.accel], max_leaf=a.max_leaf)
     t_commit = time.time() - t0
     cam = make_camera(sc.camera, a.width, a.height)
     npix = a.width * a.height
@@ -305,7 +305,7 @@ def run_b200(a):
             "vs_baseline": value / PUBLISHED_SPP_S if a.scene == "cornell-box" else None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(a), "triangles": sc.n_triangles, "spp_per_step_per_gpu": S,
-                       "paths_per_step": S * npix * world, "accel": {"bvh4": "SAH BVH4 (128 B nodes", "bvh2": "SAH BVH2 (64 B nodes", "lbvh": "device-built LBVH4 (128 B nodes"}[a.accel] + ", FP32 outward boxes) + reference BVH for boundary hits",
+                       "paths_per_step": S * npix * world, "accel": {"bvh4": "SAH BVH4 (128 B nodes", "bvh2": "SAH BVH2 (64 B nodes", "lbvh": "device-built LBVH4 (128 B nodes", "bvh4q": "SAH BVH4, 8-bit quantised child boxes (64 B nodes"}[a.accel] + ", FP32 outward boxes) + reference BVH for boundary hits",
                        "l2": "no flush: per-step path state (212 B x 16.8 M paths = 3.6 GB) exceeds the 126 MB L2; the scene itself is L2-resident by nature",
                        "scene_create_s": t_create, "scene_commit_s": t_commit, "parallelism": f"spp-sharded x{world}, 1 NCCL reduce per step"},
             "mrays_s": float(tot[0].item()) / (ms_total * 1e-3) / 1e6,

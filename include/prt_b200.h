@@ -117,7 +117,11 @@ enum prt_accel {
      * hierarchy, bottom-up FP64 boxes, subtrees of <= max_leaf triangles collapsed into leaves. A
      * lower-quality tree than the binned-SAH one (more nodes per ray) committed in a fraction of the
      * time; same hits by the same argument. Needs a GPU context (PRT_ERR_NO_DEVICE otherwise). */
-    PRT_ACCEL_LBVH4_DEVICE = 3
+    PRT_ACCEL_LBVH4_DEVICE = 3,
+    /* PRT_ACCEL_SAH_BVH4 with the child boxes quantised to 8 bits per plane relative to the node
+     * (64-byte nodes: half the bytes per node fetch, slightly looser boxes, more decode arithmetic).
+     * Same hits: the decoded boxes contain the boxes they replace. */
+    PRT_ACCEL_SAH_BVH4Q = 4
 };
 
 typedef struct prt_build_opts {

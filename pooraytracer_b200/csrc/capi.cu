@@ -90,6 +90,7 @@ struct prt_scene {
     DevBuf<TriShade> d_shade;
     DevBuf<Node2> d_nodes2;
     DevBuf<Node4> d_nodes4;
+    DevBuf<Node4Q> d_nodes4q;
     DevBuf<RefNode> d_ref_nodes;
     DevBuf<LightTri> d_light_tris;
     DevBuf<LightNode> d_light_nodes;
@@ -321,7 +322,7 @@ void prt_scene_destroy(prt_scene* scene) {
 int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_scene_commit: null scene");
     const int accel = opts ? opts->accel : PRT_ACCEL_SAH_BVH2;
-    if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2 && accel != PRT_ACCEL_SAH_BVH4 && accel != PRT_ACCEL_LBVH4_DEVICE)
+    if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2 && accel != PRT_ACCEL_SAH_BVH4 && accel != PRT_ACCEL_LBVH4_DEVICE && accel != PRT_ACCEL_SAH_BVH4Q)
         return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
     HostScene& h = s->host;
     const bool dev_build = accel == PRT_ACCEL_LBVH4_DEVICE;
@@ -354,6 +355,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
             }
             h.nodes2.clear();
             h.nodes4.clear();
+            h.nodes4q.clear();
             h.isect_slots.clear();
             h.sah_max_leaf = max_leaf;
             h.slot_prim.assign((size_t)h.n_tris, 0);
@@ -372,6 +374,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
             s->d_tris.p = dbvh.tris; s->d_tris.n = (size_t)h.n_tris;
         } else if (accel == PRT_ACCEL_SAH_BVH2) h.build_sah_bvh2(default_host_threads(), max_leaf);
         else if (accel == PRT_ACCEL_SAH_BVH4) h.build_sah_bvh4(default_host_threads(), max_leaf);
+        else if (accel == PRT_ACCEL_SAH_BVH4Q) { h.build_sah_bvh4(default_host_threads(), max_leaf); h.quantise_bvh4(); }
         else h.use_reference_slots();
         h.flatten_reference_world();
     } catch (const std::bad_alloc&) {
@@ -379,10 +382,11 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     }
     s->accel = accel;
     const bool wide4 = accel == PRT_ACCEL_SAH_BVH4 || dev_build;
-    s->stats.node_bytes = accel == PRT_ACCEL_SAH_BVH2 ? PRT_NODE2_BYTES : (wide4 ? PRT_NODE4_BYTES : PRT_REFNODE_BYTES);
+    const bool quant = accel == PRT_ACCEL_SAH_BVH4Q;
+    s->stats.node_bytes = accel == PRT_ACCEL_SAH_BVH2 ? PRT_NODE2_BYTES : (wide4 ? PRT_NODE4_BYTES : (quant ? PRT_NODE4Q_BYTES : PRT_REFNODE_BYTES));
     s->stats.tri_bytes = PRT_TRI_BYTES;
     s->stats.n_nodes = accel == PRT_ACCEL_SAH_BVH2 ? (int64_t)h.nodes2.size()
-                                                   : (dev_build ? dbvh.n_nodes4 : (accel == PRT_ACCEL_SAH_BVH4 ? (int64_t)h.nodes4.size() : (int64_t)h.ref_flat.size()));
+                                                   : (dev_build ? dbvh.n_nodes4 : (accel == PRT_ACCEL_SAH_BVH4 || quant ? (int64_t)h.nodes4.size() : (int64_t)h.ref_flat.size()));
     s->stats.n_triangles = h.n_tris;
     s->device_build_ms = dbvh.build_ms;
     s->stats.build_ms = dbvh.build_ms;
@@ -422,6 +426,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     }
     CUDA_TRY(s->d_shade.upload(h.shade, st));
     CUDA_TRY(s->d_nodes2.upload(h.nodes2, st));
+    if (quant) CUDA_TRY(s->d_nodes4q.upload(h.nodes4q, st));
     CUDA_TRY(s->d_ref_nodes.upload(h.ref_flat, st));
     CUDA_TRY(s->d_light_tris.upload(h.light_tris, st));
     CUDA_TRY(s->d_light_nodes.upload(h.light_nodes, st));
@@ -441,6 +446,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     D.shade = s->d_shade.p;
     D.nodes2 = accel == PRT_ACCEL_SAH_BVH2 && !h.nodes2.empty() ? s->d_nodes2.p : nullptr;
     D.nodes4 = (accel == PRT_ACCEL_SAH_BVH4 && !h.nodes4.empty()) || (dev_build && h.n_tris > 0) ? s->d_nodes4.p : nullptr;
+    D.nodes4q = quant && !h.nodes4q.empty() ? s->d_nodes4q.p : nullptr;
     D.ref_nodes = s->d_ref_nodes.p;
     D.ref_root = h.ref_root_flat;
     D.n_nodes2 = (int32_t)h.nodes2.size();

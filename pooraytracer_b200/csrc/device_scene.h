@@ -72,6 +72,22 @@ struct alignas(128) Node4 {
     int32_t pad[4];
 };
 
+/* The BVH4 with QUANTISED child boxes: 64 bytes = half an L2 line = two 256-bit loads (the traversal
+ * kernels are bound by L1TEX requests, every lane fetching its own node). A child's plane on axis k is
+ * origin[k] + q * 2^(exp_k - 127), q in 0..255: lows rounded down, highs rounded up on the host, checked
+ * in double against the FP64 boxes, so the decoded box contains the Node4 box it was made from. Byte c
+ * of qlo[k] / qhi[k] belongs to child c. Child references as in Node4. */
+#define PRT_NODE4Q_BYTES 64
+struct alignas(64) Node4Q {
+    float origin[3];
+    uint32_t exps;    /* byte k: biased exponent of axis k's step (0: step 0, a flat axis) */
+    uint32_t qlo[3];
+    uint32_t pad0;
+    uint32_t qhi[3];
+    uint32_t pad1;
+    int32_t child[4];
+};
+
 /* The reference's own median-split BVH, flattened (Source/BVH.cpp:7-48): FP64 box, children in the
  * reference's left/right order. ref >= 0: node; ref < 0: ~slot of a triangle. */
 #define PRT_REFNODE_BYTES 64
@@ -106,6 +122,7 @@ struct DevScene {
     const TriShade* shade;     /* [n_tris] prim order */
     const Node2* nodes2;       /* SAH BVH2 (root = 0) or nullptr */
     const Node4* nodes4;       /* SAH BVH4 (root = 0) or nullptr */
+    const Node4Q* nodes4q;     /* quantised BVH4 (root = 0) or nullptr */
     const RefNode* ref_nodes;  /* reference BVH */
     int32_t ref_root;          /* -1: empty world */
     int32_t n_nodes2;

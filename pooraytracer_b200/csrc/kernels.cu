@@ -786,28 +786,32 @@ static int persistent_grid(K kernel, int block, const LaunchConfig& lc, int64_t 
         auto KERNEL = NAME<C, W>;                     \
         KERNEL<<<(GRID), 128, 0, st>>> ARGS;          \
     } while (0)
+/* wide: 2 = Node2 (or the reference tree), 4 = Node4, 40 = Node4Q */
 #define PRT_DISPATCH(count, wide, NAME, GRID, ARGS)                            \
     do {                                                                       \
         if (count) {                                                           \
-            if (wide) PRT_DISPATCH_ONE(true, 4, NAME, GRID, ARGS);             \
+            if ((wide) == 40) PRT_DISPATCH_ONE(true, 40, NAME, GRID, ARGS);    \
+            else if ((wide) == 4) PRT_DISPATCH_ONE(true, 4, NAME, GRID, ARGS); \
             else PRT_DISPATCH_ONE(true, 2, NAME, GRID, ARGS);                  \
         } else {                                                               \
-            if (wide) PRT_DISPATCH_ONE(false, 4, NAME, GRID, ARGS);            \
+            if ((wide) == 40) PRT_DISPATCH_ONE(false, 40, NAME, GRID, ARGS);   \
+            else if ((wide) == 4) PRT_DISPATCH_ONE(false, 4, NAME, GRID, ARGS);\
             else PRT_DISPATCH_ONE(false, 2, NAME, GRID, ARGS);                 \
         }                                                                      \
     } while (0)
+static inline int wide_of(const DevScene& S) { return S.nodes4q ? 40 : (S.nodes4 ? 4 : 2); }
 
 void launch_trace_closest(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
                           int32_t* prim, double* t, double* alpha, double* beta, const int32_t* order, int32_t* fetch,
                           unsigned long long* counters, const LaunchConfig& lc, cudaStream_t st) {
     if (n <= 0) return;
-    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_closest, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, prim, t, alpha, beta, order, fetch, counters));
+    PRT_DISPATCH(counters != nullptr, wide_of(S), k_trace_closest, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, prim, t, alpha, beta, order, fetch, counters));
 }
 void launch_trace_any(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
                       uint8_t* hit, const int32_t* order, int32_t* fetch, unsigned long long* counters, const LaunchConfig& lc,
                       cudaStream_t st) {
     if (n <= 0) return;
-    PRT_DISPATCH(counters != nullptr, S.nodes4 != nullptr, k_trace_any, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, hit, order, fetch, counters));
+    PRT_DISPATCH(counters != nullptr, wide_of(S), k_trace_any, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, hit, order, fetch, counters));
 }
 void launch_query_sort(int64_t n, const double* o, const double* d, const float* key_lo, const float* key_scale, uint16_t* keys,
                        int32_t* hist, int32_t* cursor, int32_t* order, const LaunchConfig& lc, cudaStream_t st) {
@@ -833,7 +837,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int n_bounces = rc.max_depth + 1;
     cudaMemsetAsync(pb.ctrl, 0, sizeof(BounceCtrl) * (size_t)(n_bounces + 1), st);
     const bool count = (rc.flags & PRT_RENDER_COUNTERS) != 0;
-    const bool wide = S.nodes4 != nullptr;
+    const int wide = wide_of(S);
     LaunchConfig shade_lc = lc;
     shade_lc.trace_blocks_per_sm = 0;
     const int g_shade0 = persistent_grid(k_shade<CLS_LAMBERT>, 128, shade_lc, rc.n_paths);
@@ -890,8 +894,8 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         PathBuffers pb_ = pb;
         const uint8_t* pc_ = prim_class;
         void* args[] = {(void*)&S_, (void*)&pc_, (void*)&rc_, (void*)&pb_, (void*)&first};
-        const void* fn = count ? (wide ? (const void*)k_tail<true, 4> : (const void*)k_tail<true, 2>)
-                               : (wide ? (const void*)k_tail<false, 4> : (const void*)k_tail<false, 2>);
+        const void* fn = count ? (wide == 40 ? (const void*)k_tail<true, 40> : (wide == 4 ? (const void*)k_tail<true, 4> : (const void*)k_tail<true, 2>))
+                               : (wide == 40 ? (const void*)k_tail<false, 40> : (wide == 4 ? (const void*)k_tail<false, 4> : (const void*)k_tail<false, 2>));
         static std::unordered_map<const void*, int> occ;
         int per_sm;
         auto it = occ.find(fn);

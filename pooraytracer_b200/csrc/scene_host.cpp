@@ -572,6 +572,7 @@ static void finish_slots(HostScene& s) {
 void HostScene::build_sah_bvh2(int n_threads, int max_leaf) {
     nodes2.clear();
     nodes4.clear();
+    nodes4q.clear();
     slot_prim.clear();
     prim_slot.assign((size_t)n_tris, -1);
     if (max_leaf < 1) max_leaf = 1;
@@ -636,6 +637,7 @@ void HostScene::build_sah_bvh2(int n_threads, int max_leaf) {
 void HostScene::build_sah_bvh4(int n_threads, int max_leaf) {
     nodes2.clear();
     nodes4.clear();
+    nodes4q.clear();
     slot_prim.clear();
     prim_slot.assign((size_t)n_tris, -1);
     if (max_leaf < 1) max_leaf = 1;
@@ -711,9 +713,72 @@ void HostScene::build_sah_bvh4(int n_threads, int max_leaf) {
     finish_slots(*this);
 }
 
+/* Node4 -> Node4Q. Per node and axis: origin = the smallest child low (already an outward-rounded
+ * float), step = the smallest power of two with 255 steps covering the node's extent, lows floored,
+ * highs ceiled; every decoded plane is then checked in double against the plane it replaces and moved
+ * one more step outward if rounding got in the way. */
+void HostScene::quantise_bvh4() {
+    nodes4q.assign(nodes4.size(), Node4Q());
+    for (size_t n = 0; n < nodes4.size(); ++n) {
+        const Node4& N = nodes4[n];
+        Node4Q Q;
+        std::memset(&Q, 0, sizeof(Q));
+        for (int c = 0; c < 4; ++c) Q.child[c] = N.child[c];
+        const int32_t NO_CHILD = INT32_MIN;
+        for (int k = 0; k < 3; ++k) {
+            double lo = std::numeric_limits<double>::infinity(), hi = -std::numeric_limits<double>::infinity();
+            for (int c = 0; c < 4; ++c)
+                if (N.child[c] != NO_CHILD) {
+                    lo = std::min(lo, (double)N.lo[k][c]);
+                    hi = std::max(hi, (double)N.hi[k][c]);
+                }
+            if (!(lo <= hi)) { lo = 0.0; hi = 0.0; }
+            const float origin = (float)lo; /* exact: a float */
+            Q.origin[k] = origin;
+            const double extent = hi - (double)origin;
+            int e = 0; /* biased exponent byte; 0 = step 0 */
+            double step = 0.0;
+            if (extent > 0.0 && std::isfinite(extent)) {
+                int ex;
+                std::frexp(extent / 255.0, &ex); /* extent / 255 = m 2^ex, m in [0.5, 1) -> 2^ex >= extent / 255 */
+                e = ex + 127;
+                if (e < 1) e = 1;
+                if (e > 254) e = 254;
+                step = std::ldexp(1.0, e - 127);
+                while (255.0 * step < extent && e < 254) { ++e; step = std::ldexp(1.0, e - 127); }
+            } else if (!std::isfinite(extent)) {
+                e = 254;
+                step = std::ldexp(1.0, e - 127);
+            }
+            Q.exps |= (uint32_t)e << (8 * k);
+            for (int c = 0; c < 4; ++c) {
+                uint32_t ql = 255u, qh = 0u; /* unused child (the traversal masks it by its reference) */
+                if (N.child[c] != NO_CHILD && step > 0.0) {
+                    double a = std::floor(((double)N.lo[k][c] - (double)origin) / step);
+                    double b = std::ceil(((double)N.hi[k][c] - (double)origin) / step);
+                    if (a < 0.0) a = 0.0;
+                    if (a > 255.0) a = 255.0;
+                    if (b < 0.0) b = 0.0;
+                    if (b > 255.0) b = 255.0;
+                    while (a > 0.0 && (double)origin + a * step > (double)N.lo[k][c]) a -= 1.0;
+                    while (b < 255.0 && (double)origin + b * step < (double)N.hi[k][c]) b += 1.0;
+                    ql = (uint32_t)a;
+                    qh = (uint32_t)b;
+                } else if (N.child[c] != NO_CHILD) {
+                    ql = 0u; qh = 0u; /* flat axis: every plane is the origin */
+                }
+                Q.qlo[k] |= ql << (8 * c);
+                Q.qhi[k] |= qh << (8 * c);
+            }
+        }
+        nodes4q[n] = Q;
+    }
+}
+
 void HostScene::use_reference_slots() {
     nodes2.clear();
     nodes4.clear();
+    nodes4q.clear();
     slot_prim.assign((size_t)n_tris, 0);
     prim_slot.assign((size_t)n_tris, -1);
     for (int64_t p = 0; p < n_tris; ++p) {

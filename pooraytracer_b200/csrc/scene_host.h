@@ -74,6 +74,7 @@ struct HostScene {
     /* committed acceleration structure */
     std::vector<Node2> nodes2;         /* SAH BVH2 */
     std::vector<Node4> nodes4;         /* SAH BVH4 (collapsed BVH2) */
+    std::vector<Node4Q> nodes4q;       /* nodes4 with quantised child boxes (PRT_ACCEL_SAH_BVH4Q) */
     std::vector<int32_t> slot_prim;    /* slot -> prim */
     std::vector<int32_t> prim_slot;    /* prim -> slot */
     std::vector<TriIsect> isect_slots; /* isect permuted into slot order */
@@ -87,6 +88,7 @@ struct HostScene {
     void build_reference_bvhs(int n_threads);
     void build_sah_bvh2(int n_threads, int max_leaf);
     void build_sah_bvh4(int n_threads, int max_leaf);
+    void quantise_bvh4(); /* nodes4 -> nodes4q */
     /* slot order = reference DFS order, no SAH tree (PRT_ACCEL_REFERENCE_BVH2) */
     void use_reference_slots();
     void flatten_reference_world();

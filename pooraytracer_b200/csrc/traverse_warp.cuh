@@ -61,6 +61,8 @@ namespace prt {
 
 struct RayF32 { /* the FP32 side of a ray, for box tests only: t = b * inv - o * inv */
     float ix, iy, iz;    /* fl32(1 / d), clamped */
+    float o32x, o32y, o32z; /* fl32(o): the quantised-node decode works relative to the node's origin */
+    float ex, ey, ez;       /* |o32| |inv32| 2^-22 per axis (rounded up) + a denormal-scale floor */
 #if PRT_BOX_AXIS_ERR
     float nx, ny, nz;    /* o32 * inv32 + err(axis), rounded up: subtracted from the NEAR plane's product */
     float fx, fy, fz;    /* o32 * inv32 - err(axis), rounded down: subtracted from the FAR plane's product */
@@ -82,6 +84,8 @@ __device__ __forceinline__ RayF32 make_ray_f32(d3 o, d3 d) {
     const float ex = __fmul_ru(__fmul_ru(fabsf(ox), fabsf(r.ix)), 2.3841858e-7f); /* |o32| |inv32| 2^-22 */
     const float ey = __fmul_ru(__fmul_ru(fabsf(oy), fabsf(r.iy)), 2.3841858e-7f);
     const float ez = __fmul_ru(__fmul_ru(fabsf(oz), fabsf(r.iz)), 2.3841858e-7f);
+    r.o32x = ox; r.o32y = oy; r.o32z = oz;
+    r.ex = ex + 1e-36f; r.ey = ey + 1e-36f; r.ez = ez + 1e-36f;
 #if PRT_BOX_AXIS_ERR
     const float px = ox * r.ix, py = oy * r.iy, pz = oz * r.iz;
     r.nx = __fadd_ru(px, ex); r.ny = __fadd_ru(py, ey); r.nz = __fadd_ru(pz, ez);
@@ -122,6 +126,45 @@ __device__ __forceinline__ bool box_f32(float lx, float ly, float lz, float hx, 
     entry = fmaxf(fmaf(-PRT_BOX_EPS, fabsf(E), E) - r.err, tmin32);
     const float exit = fminf(fmaf(PRT_BOX_EPS, fabsf(X), X) + r.err, tbest32);
 #endif
+    return entry <= exit;
+}
+
+/* Quantised nodes (Node4Q). A plane is origin + q s with s = 2^(exp - 127), so along one axis
+ *     t = (origin + q s - o) / d = q (s inv) + (origin - o) inv =: q A + B.
+ * A = s inv32 is exact (a power of two times a float), D = fl(origin - o32), B = fl(D inv32), and the
+ * plane's t comes out of ONE fma. With e_i the roundings (|e_i| <= 2^-24):
+ *     |t_c - t*| <= |t_c| 2^-23 + |B| 2^-22 + |o| |inv| 2^-24 (1 + 2^-23),
+ * covered by the relative pad of the final entry / exit (2^-21 |E|, as for Node4), by
+ * pad(axis) = |B| 2^-21 + err(axis) folded into B per node and axis (near: B - pad rounded down, far:
+ * B + pad rounded up; err(axis) = |o32| |inv32| 2^-22 + 1e-36), each with a margin of 2x or more.
+ * Three words per axis carry the four children's bytes, so the near / far plane of an axis is ONE
+ * select per node, not per child. */
+struct QuantAxis {
+    float A, Bn, Bf;
+    uint32_t wn, wf; /* the four children's near / far plane bytes */
+};
+__device__ __forceinline__ QuantAxis quant_axis(float origin, uint32_t exp_byte, uint32_t qlo, uint32_t qhi, float o32, float inv, float err) {
+    QuantAxis a;
+    const float s = __uint_as_float(exp_byte << 23);
+    a.A = s * inv;
+    const float B = (origin - o32) * inv;
+    const float pad = fmaf(fabsf(B), PRT_BOX_EPS, err);
+    a.Bn = __fadd_rd(B, -pad);
+    a.Bf = __fadd_ru(B, pad);
+    const bool neg = inv < 0.f;
+    a.wn = neg ? qhi : qlo;
+    a.wf = neg ? qlo : qhi;
+    return a;
+}
+template <int C>
+__device__ __forceinline__ bool box_quant(const QuantAxis& x, const QuantAxis& y, const QuantAxis& z, float tmin32, float tbest32, float& entry) {
+    const float nx = fmaf((float)((x.wn >> (8 * C)) & 255u), x.A, x.Bn), fx = fmaf((float)((x.wf >> (8 * C)) & 255u), x.A, x.Bf);
+    const float ny = fmaf((float)((y.wn >> (8 * C)) & 255u), y.A, y.Bn), fy = fmaf((float)((y.wf >> (8 * C)) & 255u), y.A, y.Bf);
+    const float nz = fmaf((float)((z.wn >> (8 * C)) & 255u), z.A, z.Bn), fz = fmaf((float)((z.wf >> (8 * C)) & 255u), z.A, z.Bf);
+    const float E = fmaxf(fmaxf(nx, ny), nz);
+    const float X = fminf(fminf(fx, fy), fz);
+    entry = fmaxf(fmaf(-PRT_BOX_EPS, fabsf(E), E), tmin32);
+    const float exit = fminf(fmaf(PRT_BOX_EPS, fabsf(X), X), tbest32);
     return entry <= exit;
 }
 
@@ -186,7 +229,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     RayF32 rf = make_ray_f32(o, d);
     Hit hit;
     hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
-    const bool use_sah = WIDE == 4 ? S.nodes4 != nullptr : S.nodes2 != nullptr;
+    const bool use_sah = WIDE == 40 ? S.nodes4q != nullptr : (WIDE == 4 ? S.nodes4 != nullptr : S.nodes2 != nullptr);
 
     /* fetch pipeline state (c_*, b_base, b_pref are warp-uniform) */
     int32_t a_raw = 0;                 /* lane 0: chunk A's atomic result */
@@ -369,25 +412,41 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
             for (;;) {
                 if (cur >= 0 && cur != PRT_DONE) {
                     if (COUNT) cnt.nodes++;
-                    if (WIDE == 4) {
+                    if (WIDE == 4 || WIDE == 40) {
+                        float e0, e1, e2, e3;
+                        bool h0, h1, h2, h3;
+                        int4 ch;
+                        if (WIDE == 40) {
+                            const char* __restrict__ p = reinterpret_cast<const char*>(S.nodes4q + cur);
+                            const f8 q0 = ld256f(p), q1 = ld256f(p + 32);
+                            const uint32_t exps = __float_as_uint(q0.v[3]);
+                            const QuantAxis ax = quant_axis(q0.v[0], exps & 255u, __float_as_uint(q0.v[4]), __float_as_uint(q1.v[0]), rf.o32x, rf.ix, rf.ex);
+                            const QuantAxis ay = quant_axis(q0.v[1], (exps >> 8) & 255u, __float_as_uint(q0.v[5]), __float_as_uint(q1.v[1]), rf.o32y, rf.iy, rf.ey);
+                            const QuantAxis az = quant_axis(q0.v[2], (exps >> 16) & 255u, __float_as_uint(q0.v[6]), __float_as_uint(q1.v[2]), rf.o32z, rf.iz, rf.ez);
+                            ch = make_int4(__float_as_int(q1.v[4]), __float_as_int(q1.v[5]), __float_as_int(q1.v[6]), __float_as_int(q1.v[7]));
+                            h0 = box_quant<0>(ax, ay, az, tmin32, tbest32, e0) && ch.x != PRT_NO_CHILD;
+                            h1 = box_quant<1>(ax, ay, az, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
+                            h2 = box_quant<2>(ax, ay, az, tmin32, tbest32, e2) && ch.z != PRT_NO_CHILD;
+                            h3 = box_quant<3>(ax, ay, az, tmin32, tbest32, e3) && ch.w != PRT_NO_CHILD;
+                        } else {
 #if PRT_LD256
                         const char* __restrict__ p = reinterpret_cast<const char*>(S.nodes4 + cur);
                         const f8 q0 = ld256f(p), q1 = ld256f(p + 32), q2 = ld256f(p + 64), q3 = ld256f(p + 96);
                         const float4 lx = make_float4(q0.v[0], q0.v[1], q0.v[2], q0.v[3]), ly = make_float4(q0.v[4], q0.v[5], q0.v[6], q0.v[7]);
                         const float4 lz = make_float4(q1.v[0], q1.v[1], q1.v[2], q1.v[3]), hx = make_float4(q1.v[4], q1.v[5], q1.v[6], q1.v[7]);
                         const float4 hy = make_float4(q2.v[0], q2.v[1], q2.v[2], q2.v[3]), hz = make_float4(q2.v[4], q2.v[5], q2.v[6], q2.v[7]);
-                        const int4 ch = make_int4(__float_as_int(q3.v[0]), __float_as_int(q3.v[1]), __float_as_int(q3.v[2]), __float_as_int(q3.v[3]));
+                        ch = make_int4(__float_as_int(q3.v[0]), __float_as_int(q3.v[1]), __float_as_int(q3.v[2]), __float_as_int(q3.v[3]));
 #else
                         const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes4 + cur);
                         const float4 lx = __ldg(p), ly = __ldg(p + 1), lz = __ldg(p + 2);
                         const float4 hx = __ldg(p + 3), hy = __ldg(p + 4), hz = __ldg(p + 5);
-                        const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 6));
+                        ch = __ldg(reinterpret_cast<const int4*>(p + 6));
 #endif
-                        float e0, e1, e2, e3;
-                        const bool h0 = box_f32(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, rf, tmin32, tbest32, e0);
-                        const bool h1 = box_f32(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
-                        const bool h2 = box_f32(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, rf, tmin32, tbest32, e2) && ch.z != PRT_NO_CHILD;
-                        const bool h3 = box_f32(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, rf, tmin32, tbest32, e3) && ch.w != PRT_NO_CHILD;
+                        h0 = box_f32(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, rf, tmin32, tbest32, e0);
+                        h1 = box_f32(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
+                        h2 = box_f32(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, rf, tmin32, tbest32, e2) && ch.z != PRT_NO_CHILD;
+                        h3 = box_f32(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, rf, tmin32, tbest32, e3) && ch.w != PRT_NO_CHILD;
+                        }
                         /* sort the hit children by entry distance: key = distance bits (non-negative
                          * float: ordered like an unsigned) with the child's slot in the two low bits */
                         const unsigned MISS = 0xffffffffu;

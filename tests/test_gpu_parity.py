@@ -19,7 +19,7 @@ from pooraytracer_b200 import Scene, _capi as capi, make_camera, make_params, sc
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-ACCELS = [capi.ACCEL_SAH_BVH2, capi.ACCEL_SAH_BVH4, capi.ACCEL_REFERENCE_BVH2, capi.ACCEL_LBVH4_DEVICE]
+ACCELS = [capi.ACCEL_SAH_BVH2, capi.ACCEL_SAH_BVH4, capi.ACCEL_REFERENCE_BVH2, capi.ACCEL_LBVH4_DEVICE, capi.ACCEL_SAH_BVH4Q]
 
 
 def gold(name):

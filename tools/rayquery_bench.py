@@ -25,7 +25,7 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--check", type=int, default=0, help="compare the first N rays with the CPU oracle")
     ap.add_argument("--max-leaf", type=int, default=0)
-    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4", "lbvh"])
+    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4", "lbvh", "bvh4q"])
     a = ap.parse_args()
     import torch
     from pooraytracer_b200 import Context, Scene, _capi as capi, scenes
@@ -42,7 +42,7 @@ def main():
     t0 = time.time()
     import ctypes as C
     o_ = capi.PrtBuildOpts()
-    o_.accel = {"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE}[a.accel]
+    o_.accel = {"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE, "bvh4q": capi.ACCEL_SAH_BVH4Q}[a.accel]
     o_.reserved[0] = a.max_leaf
     rc = scene.lib.prt_scene_commit(scene.handle, C.byref(o_))
     assert rc == 0, scene.lib.prt_last_error()
