@@ -43,6 +43,10 @@ namespace prt {
 #ifndef PRT_LEAF_GATE
 #define PRT_LEAF_GATE 16         /* lanes that must hold a parked leaf before the triangle block runs */
 #endif
+#ifndef PRT_SAH_STACK
+#define PRT_SAH_STACK 64         /* entries of the SAH / LBVH walk's stack; a ray that overflows it is handed to the
+                                    reference-order walk (whose own depth is bounded by log2 of the mesh sizes) */
+#endif
 #ifndef PRT_REFILL_BELOW
 #define PRT_REFILL_BELOW 16      /* refill idle lanes once fewer than this many lanes hold a ray */
 #endif
@@ -214,7 +218,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
-    int32_t stack[PRT_STACK];
+    int32_t stack[PRT_SAH_STACK];
     int sp = 0;
     int32_t cur = PRT_DONE;
     int32_t leaf = -1; /* PRT_WALK_MODE 1: parked leaf, (slot << 3) | (triangles left - 1) */
@@ -223,6 +227,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     unsigned long long dbg_start = 0;
 #endif
     bool has_ray = false, exhausted = false, recheck = false;
+    bool overflow = false; /* a child did not fit the stack: the SAH walk is incomplete, the reference walk decides */
     d3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
     double tmin = 0.0, tmax = 0.0, tbest = 0.0;
     float tmin32 = 0.f, tbest32 = 0.f;
@@ -253,7 +258,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
         }
 #endif
         if (finished) {
-            if (recheck) {
+            if (recheck || overflow) {
                 const unsigned long long before = cnt.nodes + cnt.tris;
                 trace_reference_cold<ANY, COUNT>(S, o, d, tmin, tmax, hit, cnt);
                 if (COUNT) {
@@ -306,6 +311,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
 #endif
                     has_ray = true;
                     recheck = false;
+                    overflow = false;
                     hit.slot = -1; hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
                     tbest = tmax;
                     sp = 0;
@@ -356,7 +362,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                 const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
                 if (h0 && h1) {
                     const bool swap = e1 < e0;
-                    if (sp < PRT_STACK) stack[sp++] = swap ? ch.x : ch.y;
+                    if (sp < PRT_SAH_STACK) stack[sp++] = swap ? ch.x : ch.y; else overflow = true;
                     cur = swap ? ch.y : ch.x;
                 } else if (h0) {
                     cur = ch.x;
@@ -461,9 +467,9 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                         if (s0 == MISS) {
                             cur = sp > 0 ? stack[--sp] : PRT_DONE;
                         } else {
-                            if (s3 != MISS && sp < PRT_STACK) stack[sp++] = PRT_CHILD_OF(s3);
-                            if (s2 != MISS && sp < PRT_STACK) stack[sp++] = PRT_CHILD_OF(s2);
-                            if (s1 != MISS && sp < PRT_STACK) stack[sp++] = PRT_CHILD_OF(s1);
+                            if (s3 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s3); else overflow = true; }
+                            if (s2 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s2); else overflow = true; }
+                            if (s1 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s1); else overflow = true; }
                             cur = PRT_CHILD_OF(s0);
                         }
 #undef PRT_CHILD_OF
@@ -484,7 +490,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                         const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
                         if (h0 && h1) {
                             const bool swap = e1 < e0;
-                            if (sp < PRT_STACK) stack[sp++] = swap ? ch.x : ch.y;
+                            if (sp < PRT_SAH_STACK) stack[sp++] = swap ? ch.x : ch.y; else overflow = true;
                             cur = swap ? ch.y : ch.x;
                         } else if (h0) {
                             cur = ch.x;

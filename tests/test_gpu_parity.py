@@ -121,6 +121,40 @@ def test_device_built_bvh(gpu_ctx):
         assert np.array_equal(x, y)
 
 
+def test_stack_overflow_falls_back_to_the_reference_walk():
+    """A ray whose SAH / LBVH walk overflows its stack is handed to the reference-order walk instead of
+    silently losing a subtree. Checked on a build of the library with a 3-entry stack (made by
+    __graft_entry__.build()), in a child process because the library is chosen at import."""
+    import subprocess, sys, textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(root, "pooraytracer_b200", "libprt_b200_stack3.so")
+    if not os.path.exists(lib):
+        pytest.skip("libprt_b200_stack3.so not built")
+    code = textwrap.dedent("""
+        import os, sys
+        import numpy as np
+        sys.path.insert(0, os.path.join(%r, "tests")); sys.path.insert(0, %r)
+        import cases
+        from pooraytracer_b200 import Context, Scene, _capi as capi
+        ctx = Context(0)
+        for key in ("cornell", "bathroom"):
+            sc = cases.SCENES[key]()
+            o, d = cases.ray_batch(sc)
+            g = np.load(os.path.join(%r, "tests", "golden", "rays_" + key + ".npz"))
+            for accel in (capi.ACCEL_SAH_BVH2, capi.ACCEL_SAH_BVH4, capi.ACCEL_LBVH4_DEVICE, capi.ACCEL_SAH_BVH4Q):
+                s = Scene(ctx, sc, accel=accel)
+                s.set_counters(True)
+                prim, t, a, b = s.trace_closest(o, d, 1e-4, np.inf)
+                assert np.array_equal(prim, g["prim"]) and np.array_equal(t, g["t"]), (key, accel)
+                hit = s.trace_any(o, d, 1e-3, g["tmax"])
+                assert np.array_equal(hit.astype(bool), g["prim_bounded"] >= 0), (key, accel)
+        print("ok")
+    """ % (root, root, root))
+    env = dict(os.environ, PRT_B200_LIB=lib)
+    r = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-2000:]
+
+
 def test_counters_and_stats(gpu_ctx):
     sc = cases.cornell_small()
     o, d = cases.ray_batch(sc)
