@@ -144,6 +144,14 @@ typedef struct prt_camera {
                                           lines intend (Source/Camera.cpp:110-111, SampleSquare(),
                                           RandomNumberGenerator.h:65-68): pixel + (u0 - .5, u1 - .5),
                                           drawn as the first two numbers of the sample's stream    */
+#define PRT_RENDER_UNBIASED_LIGHT_PICK 16u /* OFF by default, not the reference's estimator: BVHNode::Sample
+                                          descends its area tree with p = RandomDouble() * area instead of
+                                          sqrt(RandomDouble()) * area (Source/BVH.cpp:64), so a light triangle
+                                          is picked in proportion to its area, which is what the returned
+                                          pdf = 1 / area already claims                                   */
+#define PRT_RENDER_LOBE_PROBABILITY 32u /* OFF by default, not the reference's estimator: PhoneReflectance::
+                                          Scatter divides the attenuation by the probability of the lobe it
+                                          sampled (pkd / pks, Source/Material.h:262-285,318-327)          */
 #define PRT_RENDER_COUNTERS 2u         /* count BVH node / triangle visits (prt_get_stats)       */
 #define PRT_RENDER_STAGE_TIMING 4u     /* CUDA events around the extend / shade / shadow kernels of
                                           every bounce (prt_stats.extend_ms ...); the call then

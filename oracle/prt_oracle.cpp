@@ -385,6 +385,10 @@ void traverse_sample(const Scene& s, V3 origin, Obj node, float p, HitRec& rec, 
     if (p < s.ObjArea(n.left)) traverse_sample(s, origin, n.left, p, rec, pdf, rng);
     else traverse_sample(s, origin, n.right, (float)(p - s.ObjArea(n.left)), rec, pdf, rng);
 }
+// The opt-in "corrected" estimators of a render (prt_render_params.flags: PRT_RENDER_UNBIASED_LIGHT_PICK,
+// PRT_RENDER_LOBE_PROBABILITY), set per worker thread by orc_render / orc_pixel_samples. 0 = the reference.
+static thread_local uint32_t tl_render_flags = 0;
+
 // HittableList::Sample -> BVHNode::Sample, Source/HittableList.h:44-59, Source/BVH.cpp:62-67
 void lights_sample(const Scene& s, V3 origin, HitRec& rec, double& pdf, Rng& rng) {
     const Node& top = s.nodes[s.lights_root];
@@ -394,7 +398,8 @@ void lights_sample(const Scene& s, V3 origin, HitRec& rec, double& pdf, Rng& rng
     areaSum = 0.0;
     areaSum += top.area;
     if (p0 <= areaSum) {
-        double p = std::sqrt(rng.RandomDouble()) * top.area;
+        const double u = rng.RandomDouble();
+        double p = ((tl_render_flags & PRT_RENDER_UNBIASED_LIGHT_PICK) ? u : std::sqrt(u)) * top.area;
         traverse_sample(s, origin, Obj{1, s.lights_root}, (float)p, rec, pdf, rng);
         pdf /= top.area;
     }
@@ -633,6 +638,7 @@ bool mat_scatter(const Scene& s, const Mat& m, V3 rayDir, const HitRec& rec, V3&
             }
             outDir = LocalToWorld(wi, c);
             if (pdf > 0. && wi.z > 0) att = f * wi.z / pdf;
+            if (tl_render_flags & PRT_RENDER_LOBE_PROBABILITY) att = att / (u < m.pkd ? m.pkd : m.pks);
             return true;
         }
         case PRT_MAT_MIRROR: {  // Material.h:334-363
@@ -936,6 +942,7 @@ int orc_render(void* p, const prt_camera* c, const prt_render_params* prm, int r
     parallel_for(H, nthreads, [&](int64_t jb, int64_t je, int tid) {
         Integrator I{*s, prm->max_depth, prm->sample_lights != 0, prm->russian_roulette,
                      v3(prm->background[0], prm->background[1], prm->background[2]), Counters{}};
+        tl_render_flags = prm->flags;
         Rng rng;
         rng.mode = rng_mode == ORC_RNG_COUNTER ? ORC_RNG_COUNTER : ORC_RNG_THREAD_LOCAL;
         rng.xs = orc_mix64(prm->rng_key + ORC_GOLDEN * (uint64_t)(jb + 1)) | 1ull;
@@ -955,6 +962,7 @@ int orc_render(void* p, const prt_camera* c, const prt_render_params* prm, int r
             }
         cnts[(size_t)tid].hits += I.cnt.hits;
         cnts[(size_t)tid].shadows += I.cnt.shadows;
+        tl_render_flags = 0;
     });
     auto t1 = std::chrono::steady_clock::now();
     if (info) {
@@ -979,6 +987,7 @@ int orc_pixel_samples(void* p, const prt_camera* c, const prt_render_params* prm
                  v3(prm->background[0], prm->background[1], prm->background[2]), Counters{}};
     V3 ro, rd;
     cam.GetRay(px, py, ro, rd);
+    tl_render_flags = prm->flags;
     Rng rng;
     const uint32_t pix = (uint32_t)(py * cam.W + px);
     for (int smp = sb; smp < se; ++smp) {
@@ -988,6 +997,7 @@ int orc_pixel_samples(void* p, const prt_camera* c, const prt_render_params* prm
         V3 L = I.RayColor(ro, rd, prm->max_depth, rng);
         out[3 * (smp - sb)] = L.x; out[3 * (smp - sb) + 1] = L.y; out[3 * (smp - sb) + 2] = L.z;
     }
+    tl_render_flags = 0;
     return 0;
 }
 

@@ -33,6 +33,8 @@ RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
 RENDER_STAGE_TIMING = 4
 RENDER_PIXEL_JITTER = 8
+RENDER_UNBIASED_LIGHT_PICK = 16
+RENDER_LOBE_PROBABILITY = 32
 
 LOAD_STRTOD = 1
 

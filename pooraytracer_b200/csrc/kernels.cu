@@ -527,7 +527,7 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
             if (rc.sample_lights && !m.skip_light_sampling) {
                 const double u0 = rng.next(), u1 = rng.next(), u2 = rng.next(), u3 = rng.next();
                 LightSample ls;
-                sample_lights(S, s.position, u0, u1, u2, u3, ls);
+                sample_lights(S, s.position, u0, u1, u2, u3, ls, (rc.flags & PRT_RENDER_UNBIASED_LIGHT_PICK) != 0);
                 const d3 to_light = ls.position - s.position;
                 const d3 light_dir = normalize(to_light);
                 const double distance = length(to_light);
@@ -552,7 +552,7 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
                 d3 att, out_dir;
                 bool scattered = true;
                 if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, out_dir);
-                else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, out_dir);
+                else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, out_dir, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
                 else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, out_dir);
                 else scatter_mirror(s, wo, att, out_dir);
                 /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */

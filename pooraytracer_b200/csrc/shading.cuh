@@ -69,11 +69,13 @@ struct LightSample {
     double pdf;
 };
 /* u0: HittableList.h:49 (picks the only object), u1: BVH.cpp:64, u2 u3: Triangle.cpp:86 */
-__device__ __forceinline__ void sample_lights(const DevScene& S, d3 origin, double u0, double u1, double u2, double u3, LightSample& out) {
+/* unbiased_pick (PRT_RENDER_UNBIASED_LIGHT_PICK, never the parity default): p = u1 * area instead of sqrt(u1) * area */
+__device__ __forceinline__ void sample_lights(const DevScene& S, d3 origin, double u0, double u1, double u2, double u3, LightSample& out,
+                                              bool unbiased_pick = false) {
     const double area_sum = S.lights_area;
     const double p0 = u0 * area_sum;
     (void)p0; /* p0 <= areaSum always: the single top BVHNode is chosen */
-    const double p = sqrt(u1) * area_sum;
+    const double p = (unbiased_pick ? u1 : sqrt(u1)) * area_sum;
     float pf = (float)p; /* TraverseSample takes `float p` (BVH.h:32) */
     int32_t ref = S.light_root;
     while (ref >= 0) {
@@ -170,7 +172,9 @@ __device__ __forceinline__ void scatter_lambertian(const DevScene& S, const DevM
     att = f * wi.z / pdf;
 }
 
-__device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMaterial& m, const Surface& s, d3 wo, Rng& rng, d3& att, d3& out_dir) {
+/* lobe_probability (PRT_RENDER_LOBE_PROBABILITY, never the parity default): divide by the probability of the sampled lobe */
+__device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMaterial& m, const Surface& s, d3 wo, Rng& rng, d3& att, d3& out_dir,
+                                              bool lobe_probability = false) {
     d3 wi = mk3(0, 0, 0), f = mk3(0, 0, 0);
     double pdf = 0.0;
     const double u = rng.next();
@@ -198,6 +202,7 @@ __device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMateri
     out_dir = local_to_world(wi, s);
     att = mk3(0, 0, 0);
     if (pdf > 0. && wi.z > 0) att = f * wi.z / pdf;
+    if (lobe_probability) att = att / (u < m.pkd ? m.pkd : m.pks);
 }
 
 __device__ __forceinline__ void scatter_mirror(const Surface& s, d3 wo, d3& att, d3& out_dir) {

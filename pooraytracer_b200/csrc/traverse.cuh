@@ -5,11 +5,10 @@
  *   slab_f64        AABB::Hit                       Source/AABB.cpp:38-64
  *   trace_reference BVHNode::Hit                    Source/BVH.cpp:51-61 (the reference's own tree
  *                                                   in the reference's own order: bit-exact)
- *   trace_bvh2      same hits through the SAH BVH2 with near-first ordering; hits on a triangle's
- *                   boundary (the only place where the reference's own tree can matter: equal-t
- *                   candidates, Source/Interval.h:21-23 + Source/BVH.cpp:58, and its box test's
- *                   rejection of degenerate intervals, Source/AABB.cpp:62) are re-resolved by
- *                   trace_reference.
+ *   on_boundary     the hits whose owner the reference's own tree may decide (equal-t candidates,
+ *                   Source/Interval.h:21-23 + Source/BVH.cpp:58; its box test's rejection of
+ *                   degenerate intervals, Source/AABB.cpp:62): the SAH / LBVH walks of
+ *                   traverse_warp.cuh hand those to trace_reference.
  *
  * All arithmetic is FP64 in the reference's operation order; the file is compiled with
  * -fmad=false so nothing is contracted into an FMA (the reference objects contain none).
@@ -165,35 +164,6 @@ __device__ __forceinline__ void trace_reference(const DevScene& S, d3 o, d3 d, d
     }
 }
 
-/* One child box of a Node2 against the ray: FP32 bounds (rounded outward on the host) widened to
- * FP64 and run through the reference's slab formula. Rounding is monotone, so a box that contains
- * the reference's box yields an interval that contains the reference's interval: nothing the
- * reference would have visited is culled. The one exception is the NaN of 0 * inf (a ray with a
- * zero direction component lying exactly in a face plane of the box), where the reference's ordered
- * shrink empties the interval; here such an axis puts no constraint on t (the ray is inside the
- * closed slab), and hits the reference would have lost that way lie on a triangle's boundary, which
- * is re-resolved through the reference's own tree anyway. Returns the entry distance. */
-__device__ __forceinline__ void slab_axis_conservative(double bmin, double bmax, double o, double inv, double& lo, double& hi) {
-    const double t0 = (bmin - o) * inv;
-    const double t1 = (bmax - o) * inv;
-    if (t0 < t1) {
-        if (t0 > lo) lo = t0;
-        if (t1 < hi) hi = t1;
-    } else if (t0 >= t1) { /* false for NaN: no constraint */
-        if (t1 > lo) lo = t1;
-        if (t0 < hi) hi = t0;
-    }
-}
-__device__ __forceinline__ bool child_box(float lx, float ly, float lz, float hx, float hy, float hz, d3 o, d3 inv, double tmin,
-                                          double tbest, double& entry) {
-    double lo = tmin, hi = tbest;
-    slab_axis_conservative((double)lx, (double)hx, o.x, inv.x, lo, hi);
-    slab_axis_conservative((double)ly, (double)hy, o.y, inv.y, lo, hi);
-    slab_axis_conservative((double)lz, (double)hz, o.z, inv.z, lo, hi);
-    entry = lo;
-    return !(hi <= lo);
-}
-
 /* A hit within PRT_EDGE_EPS (barycentric units) of the triangle's boundary. Only there can the
  * reference's answer depend on its own tree: (a) its box test rejects a degenerate interval
  * (`t.max <= t.min`, AABB.cpp:62), which happens for a ray that enters a leaf / ancestor box exactly
@@ -204,92 +174,6 @@ __device__ __forceinline__ bool child_box(float lx, float ly, float lz, float hx
 #define PRT_EDGE_EPS 1e-7
 __device__ __forceinline__ bool on_boundary(double alpha, double beta) {
     return alpha < PRT_EDGE_EPS || beta < PRT_EDGE_EPS || 1.0 - (alpha + beta) < PRT_EDGE_EPS;
-}
-
-/* SAH BVH2, near child first. `recheck` is set when the answer could depend on the reference's own
- * tree (see on_boundary): the caller then asks trace_reference. Everything else is decided here:
- * the triangle arithmetic is the reference's, and the boxes only ever contain the reference's. */
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ void trace_bvh2(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, bool& recheck, VisitCounters& cnt) {
-    hit.slot = -1;
-    hit.t = 0.0; hit.alpha = 0.0; hit.beta = 0.0;
-    recheck = false;
-    if (S.n_tris == 0) return;
-    const d3 inv = mk3(1.0 / d.x, 1.0 / d.y, 1.0 / d.z);
-    int32_t stack[PRT_STACK];
-    int sp = 0;
-    int32_t cur = 0;
-    double tbest = tmax;
-    for (;;) {
-        if (cur >= 0) {
-            const float4* __restrict__ p = reinterpret_cast<const float4*>(S.nodes2 + cur);
-            const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-            const int4 ch = __ldg(reinterpret_cast<const int4*>(p + 3));
-            PRT_COUNT_NODE(cnt);
-            /* a = lo0.xyz hi0.x | b = hi0.yz lo1.xy | c = lo1.z hi1.xyz */
-            double e0, e1;
-            const bool h0 = child_box(a.x, a.y, a.z, a.w, b.x, b.y, o, inv, tmin, tbest, e0);
-            const bool h1 = child_box(b.z, b.w, c.x, c.y, c.z, c.w, o, inv, tmin, tbest, e1) && ch.y != PRT_NO_CHILD;
-            if (h0 && h1) {
-                const bool swap = e1 < e0;
-                const int32_t near_c = swap ? ch.y : ch.x, far_c = swap ? ch.x : ch.y;
-                if (sp < PRT_STACK) stack[sp++] = far_c;
-                cur = near_c;
-                continue;
-            }
-            if (h0) { cur = ch.x; continue; }
-            if (h1) { cur = ch.y; continue; }
-        } else {
-            const int32_t code = ~cur;
-            const int32_t first = code >> 3, count = (code & 7) + 1;
-            for (int32_t i = 0; i < count; ++i) {
-                double t, al, be;
-                PRT_COUNT_TRI(cnt);
-                if (tri_test(S.tris + first + i, o, d, tmin, tbest, t, al, be)) {
-                    if (ANY) {
-                        /* a boundary hit may be one the reference's boxes reject: keep looking for
-                         * an interior one, and let the reference decide if none turns up */
-                        if (on_boundary(al, be)) { recheck = true; continue; }
-                        hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
-                        recheck = false;
-                        return;
-                    }
-                    /* two different triangles at the very same t (coplanar overlap, shared edge):
-                     * the reference's visiting order decides */
-                    recheck = hit.slot >= 0 && t == tbest;
-                    hit.slot = first + i; hit.t = t; hit.alpha = al; hit.beta = be;
-                    tbest = t;
-                }
-            }
-        }
-        if (sp == 0) break;
-        cur = stack[--sp];
-    }
-    if (!ANY && hit.slot >= 0 && on_boundary(hit.alpha, hit.beta)) recheck = true;
-}
-
-/* closest hit through whichever structure is committed; result identical to the reference's */
-template <bool COUNT>
-__device__ __forceinline__ void closest_hit(const DevScene& S, d3 o, d3 d, double tmin, double tmax, Hit& hit, VisitCounters& cnt) {
-    if (S.nodes2) {
-        bool recheck;
-        trace_bvh2<false, COUNT>(S, o, d, tmin, tmax, hit, recheck, cnt);
-        if (recheck) trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-    } else {
-        trace_reference<false, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-    }
-}
-template <bool COUNT>
-__device__ __forceinline__ bool any_hit(const DevScene& S, d3 o, d3 d, double tmin, double tmax, VisitCounters& cnt) {
-    Hit hit;
-    if (S.nodes2) {
-        bool recheck;
-        trace_bvh2<true, COUNT>(S, o, d, tmin, tmax, hit, recheck, cnt);
-        if (recheck) trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-    } else {
-        trace_reference<true, COUNT>(S, o, d, tmin, tmax, hit, cnt);
-    }
-    return hit.slot >= 0;
 }
 
 }  // namespace prt

@@ -167,3 +167,41 @@ def test_pixel_jitter_is_opt_in_and_integrates_the_pixel():
     assert not np.array_equal(centre, jit)
     assert abs(float(jit.mean()) - float(fine.mean())) < 0.05 * float(fine.mean())
     assert abs(float(centre.mean()) - float(fine.mean())) > 0.15 * float(fine.mean())
+
+
+def test_corrected_estimators_are_opt_in_and_do_what_they_claim():
+    """SURVEY 8 f4 switches in the port, both OFF by default (the golden renders pin the default):
+    PRT_RENDER_LOBE_PROBABILITY — furnace test: a Phong plane with kd = 0.5, ks = 0, Ns = 50 under a white sky,
+    one bounce, no roulette. The reference's Scatter picks the (black) specular lobe 40 % of the time without
+    dividing by the lobe probability and returns 0.6 kd = 0.30; corrected, the albedo 0.50.
+    PRT_RENDER_UNBIASED_LIGHT_PICK — a two-triangle quad light centred over a floor, seen from above: the
+    reference's sqrt(u) descent gives one triangle 25 % and the other 75 % of the samples, the floor is 1.3x
+    brighter on one side; corrected, the two halves agree."""
+    from pooraytracer_b200 import _capi as capi
+    from pooraytracer_b200.scenes import _Builder, Material, quad
+    b = _Builder("furnace")
+    m = b.material(Material("material1", capi.MAT_PHONG, kd=(0.5, 0.5, 0.5), ks=(0.0, 0.0, 0.0), ns=50.0))
+    b.mesh("plane", m, *quad((-50, 0, 50), (50, 0, 50), (50, 0, -50), (-50, 0, -50)))
+    sc = b.build(dict(width=16, height=16, fovy=20.0, eye=(0, 3, 0.5), look_at=(0, 0, 0), up=(0, 1, 0)))
+    O = ol.OracleScene("orc", sc, ol.DEFINE_UB)
+    cam = make_camera(sc.camera, 16, 16)
+    mean = {}
+    for fl in (0, capi.RENDER_LOBE_PROBABILITY):
+        img, _ = O.render(cam, make_params(256, 1, sample_lights=False, rr=1.0, rng_key=3, background=(1, 1, 1), flags=fl))
+        mean[fl] = float(img.mean())
+    assert abs(mean[0] - 0.30) < 0.01 and abs(mean[capi.RENDER_LOBE_PROBABILITY] - 0.50) < 0.01, mean
+
+    b = _Builder("sym")
+    wh = b.material(Material("DiffuseWhite", capi.MAT_LAMBERTIAN, kd=(0.7, 0.7, 0.7)))
+    li = b.material(Material("Light", capi.MAT_DIFFUSE_LIGHT, emission=(10.0, 10.0, 10.0)))
+    b.mesh("floor", wh, *quad((-2, 0, 2), (2, 0, 2), (2, 0, -2), (-2, 0, -2)))
+    b.mesh("light", li, *quad((-1, 1, -0.2), (1, 1, -0.2), (1, 1, 0.2), (-1, 1, 0.2)))
+    sc = b.build(dict(width=32, height=16, fovy=60.0, eye=(0, 4, 0.001), look_at=(0, 0, 0), up=(0, 0, -1)))
+    O = ol.OracleScene("orc", sc, ol.DEFINE_UB)
+    cam = make_camera(sc.camera, 32, 16)
+    ratio = {}
+    for fl in (0, capi.RENDER_UNBIASED_LIGHT_PICK):
+        img, _ = O.render(cam, make_params(256, 1, sample_lights=True, rr=1.0, rng_key=3, flags=fl))
+        floor = img[..., 0] < 5  # not the light itself
+        ratio[fl] = float(img[:, :16, 0][floor[:, :16]].mean() / img[:, 16:, 0][floor[:, 16:]].mean())
+    assert ratio[0] > 1.2 and abs(ratio[capi.RENDER_UNBIASED_LIGHT_PICK] - 1.0) < 0.03, ratio
