@@ -1,3 +1,4 @@
+"""Per-step device time of bathroom2 (how the 101 .. 204 ms spread of profiles/r1_s13_grazing_rays.txt was seen)."""
 import sys, time, os
 sys.path.insert(0, '.')
 import torch

@@ -1,3 +1,6 @@
+"""Runs one workload on a -DPRT_DEBUG_SLOW_RAY=<fetches> build (tools/build_variants.sh "slowray:-DPRT_DEBUG_SLOW_RAY=1500ull",
+PRT_B200_LIB=.../lib_slowray.so): the library prints every ray whose walk fetched more records than that.
+usage: python tools/slow_ray_probe.py bath|soup|terrain"""
 import sys, os
 sys.path.insert(0, '.')
 import torch, numpy as np
