@@ -3,8 +3,8 @@
 (BASELINE.json configs[1]; the reference published 20382 s for 3000 spp = 0.1472 spp/s on an
 unstated CPU).
 
-A STEP renders a slice of `--spp-per-step` samples per pixel of that frame (default 16 = one
-wavefront pass of 16.8 M paths) through the full depth-100 pipeline; 3000 / 16 steps make the whole
+A STEP renders a slice of `--spp-per-step` samples per pixel of that frame (default 64 = one
+wavefront pass of 67 M paths, 12.9 GB of path records) through the full depth-100 pipeline; 3000 / 64 steps make the whole
 image, and throughput is intensive, so the slice measures the named configuration, not a smaller
 one. The scene files of the reference are absent (example-scenes-cg24/ is empty), so the scene is the
 procedural cornell-box of pooraytracer_b200/scenes.py in the reference's material vocabulary.
@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=64)
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--depth", type=int, default=DEPTH)
@@ -306,7 +306,7 @@ def run_b200(a):
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(a), "triangles": sc.n_triangles, "spp_per_step_per_gpu": S,
                        "paths_per_step": S * npix * world, "accel": {"bvh4": "SAH BVH4 (128 B nodes", "bvh2": "SAH BVH2 (64 B nodes", "lbvh": "device-built LBVH4 (128 B nodes", "bvh4q": "SAH BVH4, 8-bit quantised child boxes (64 B nodes"}[a.accel] + ", FP32 outward boxes) + reference BVH for boundary hits",
-                       "l2": "no flush: per-step path state (212 B x 16.8 M paths = 3.6 GB) exceeds the 126 MB L2; the scene itself is L2-resident by nature",
+                       "l2": f"no flush: per-step path state (192 B x {S * npix / 1e6:.1f} M paths = {192 * S * npix / 1e9:.1f} GB) exceeds the 126 MB L2; the scene itself is L2-resident by nature",
                        "scene_create_s": t_create, "scene_commit_s": t_commit, "parallelism": f"spp-sharded x{world}, 1 NCCL reduce per step"},
             "mrays_s": float(tot[0].item()) / (ms_total * 1e-3) / 1e6,
             "mpaths_s": a.steps * S * npix * world / (ms_total * 1e-3) / 1e6,

@@ -177,12 +177,18 @@ int ensure_sort_scratch(prt_scene* s, cudaStream_t st) {
 
 int64_t pass_path_budget() {
     const char* env = std::getenv("PRT_PASS_PATHS");
-    int64_t v = env ? std::atoll(env) : (int64_t(1) << 24);
+    int64_t v = env ? std::atoll(env) : (int64_t(1) << 26); /* 12.9 GB of path records: per-pass fixed costs (tail, drains) amortised over 4x the paths of 2^24, +9 % */
     if (v < 1024) v = 1024;
     return v;
 }
 
-int ensure_pool(prt_scene* s, int64_t cap, int n_bounces) {
+int ensure_pool(prt_scene* s, int64_t cap, int n_bounces, bool binning) {
+    if (binning && (int64_t)s->p_ke.n < cap) { /* ray-binning scratch only when PRT_SORT_MIN asks for it */
+        CUDA_TRY(s->p_ke.ensure((size_t)cap));
+        CUDA_TRY(s->p_ks.ensure((size_t)cap));
+        CUDA_TRY(s->p_qse.ensure((size_t)cap));
+        CUDA_TRY(s->p_qss.ensure((size_t)cap));
+    }
     if (cap > s->pool_cap) {
         CUDA_TRY(s->p_rec.ensure((size_t)cap));
         CUDA_TRY(s->p_q0.ensure((size_t)cap));
@@ -192,10 +198,6 @@ int ensure_pool(prt_scene* s, int64_t cap, int n_bounces) {
         CUDA_TRY(s->p_qm2.ensure((size_t)cap));
         CUDA_TRY(s->p_qm3.ensure((size_t)cap));
         CUDA_TRY(s->p_qs.ensure((size_t)cap));
-        CUDA_TRY(s->p_ke.ensure((size_t)cap));
-        CUDA_TRY(s->p_ks.ensure((size_t)cap));
-        CUDA_TRY(s->p_qse.ensure((size_t)cap));
-        CUDA_TRY(s->p_qss.ensure((size_t)cap));
         s->pool_cap = cap;
     }
     if (n_bounces + 2 > s->pool_bounces) {
@@ -652,7 +654,7 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     int per_pass = (int)std::max<int64_t>(1, budget / rcn.npix);
     per_pass = std::min(per_pass, std::max(1, se - sb));
     const int n_bounces = params->max_depth + 1;
-    rc = ensure_pool(s, (int64_t)per_pass * rcn.npix, n_bounces);
+    rc = ensure_pool(s, (int64_t)per_pass * rcn.npix, n_bounces, launch_config(s->ctx).sort_min > 0);
     if (rc) return rc;
     const bool counting = (rcn.flags & PRT_RENDER_COUNTERS) != 0;
     CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 8 * sizeof(unsigned long long), st));
