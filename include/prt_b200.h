@@ -152,6 +152,12 @@ typedef struct prt_camera {
 #define PRT_RENDER_LOBE_PROBABILITY 32u /* OFF by default, not the reference's estimator: PhoneReflectance::
                                           Scatter divides the attenuation by the probability of the lobe it
                                           sampled (pkd / pks, Source/Material.h:262-285,318-327)          */
+#define PRT_RENDER_MIS 64u             /* OFF by default, not the reference's estimator: at a vertex whose
+                                          BSDF is the cosine lobe (Lambertian, Phong with Ns <= 1) and which
+                                          samples lights, the light sample is weighted p_l / (p_l + p_b) and
+                                          an emitter met by the scattered ray — which the reference drops
+                                          (Source/Camera.cpp:187-196) — is added with p_b / (p_b + p_l)
+                                          (balance heuristic; p_b = cos / pi, p_l = dist^2 / (cos_l A))   */
 #define PRT_RENDER_COUNTERS 2u         /* count BVH node / triangle visits (prt_get_stats)       */
 #define PRT_RENDER_STAGE_TIMING 4u     /* CUDA events around the extend / shade / shadow kernels of
                                           every bounce (prt_stats.extend_ms ...); the call then

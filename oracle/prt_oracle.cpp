@@ -594,7 +594,8 @@ V3 mat_eval(const Scene& s, const Mat& m, V3 wi, const EvalCtx& c, Rng& rng) {
 
 // Material::Scatter. Returns false when the material does not scatter. `att` is pre-set to 0 by the
 // caller (defined meaning of Camera.cpp:177).
-bool mat_scatter(const Scene& s, const Mat& m, V3 rayDir, const HitRec& rec, V3& att, V3& outDir, Rng& rng) {
+bool mat_scatter(const Scene& s, const Mat& m, V3 rayDir, const HitRec& rec, V3& att, V3& outDir, Rng& rng, double* cosinePdf = nullptr) {
+    if (cosinePdf) *cosinePdf = 0.0; /* PRT_RENDER_MIS: pdf of the sampled direction where the BSDF is the cosine lobe */
     EvalCtx c;
     c.p = rec.position; c.uv = rec.uv; c.n = rec.normal; c.dpdus = rec.tangent;
     c.wo = WorldToLocal(-rayDir, rec);
@@ -606,6 +607,7 @@ bool mat_scatter(const Scene& s, const Mat& m, V3 rayDir, const HitRec& rec, V3&
             V3 f = tex_or_color(s, m.kd_tex, m.kd, c.uv) * InvPi;
             outDir = LocalToWorld(wi, c);
             att = f * wi.z / pdf;
+            if (cosinePdf) *cosinePdf = pdf;
             return true;
         }
         case PRT_MAT_PHONG: {  // Material.h:183-226,262-285
@@ -639,6 +641,7 @@ bool mat_scatter(const Scene& s, const Mat& m, V3 rayDir, const HitRec& rec, V3&
             outDir = LocalToWorld(wi, c);
             if (pdf > 0. && wi.z > 0) att = f * wi.z / pdf;
             if (tl_render_flags & PRT_RENDER_LOBE_PROBABILITY) att = att / (u < m.pkd ? m.pkd : m.pks);
+            if (cosinePdf && u < m.pkd && m.pkd == 1.0) *cosinePdf = pdf;
             return true;
         }
         case PRT_MAT_MIRROR: {  // Material.h:334-363
@@ -722,6 +725,8 @@ struct Integrator {
         return world_hit(s, o, d, dom, rec);
     }
 
+    static bool CosineLobe(const Mat& m) { return m.type == PRT_MAT_LAMBERTIAN || (m.type == PRT_MAT_PHONG && m.pkd == 1.0); }
+
     // Camera::RayColor, Source/Camera.cpp:119-204
     V3 RayColor(V3 ro, V3 rd, int depth, Rng& rng) {
         if (depth < 0.) return v3(0, 0, 0);
@@ -754,12 +759,18 @@ struct Integrator {
                 double cosTheta = localWi.z;
                 double cosThetaBar = dot(localLightNormal, -localWi);
                 direct = emission * fr * cosTheta * cosThetaBar / (distance * distance) / pdfLights;
+                if ((tl_render_flags & PRT_RENDER_MIS) && CosineLobe(m)) {
+                    const double pl = pdfLights * (distance * distance) / cosThetaBar;
+                    const double pb = cosTheta * InvPi;
+                    direct = direct * (pl / (pl + pb));
+                }
             }
         }
         V3 att = v3(0, 0, 0);
         V3 sd;
         if (rng.RandomDouble() < rr) {
-            if (mat_scatter(s, m, rd, rec, att, sd, rng)) {
+            double cosinePdf = 0.0;
+            if (mat_scatter(s, m, rd, rec, att, sd, rng, &cosinePdf)) {
                 if (sampleLights) {
                     HitRec peek;
                     if (Hit(ps, sd, Interval(0.0001, INF), peek)) {
@@ -767,6 +778,17 @@ struct Integrator {
                             scatter = att * RayColor(ps, sd, depth - 1, rng) / rr;
                         } else if (m.SkipLightSampling()) {
                             scatter = att * RayColor(ps, sd, depth - 1, rng) / rr;
+                        } else if ((tl_render_flags & PRT_RENDER_MIS) && cosinePdf > 0.0 && depth - 1 >= 0) {
+                            /* PRT_RENDER_MIS: the emitter the reference drops here, weighted against the
+                             * light sampler's density for the same point (0 for a back-facing emitter) */
+                            const Mat& em = s.mats[peek.mat];
+                            const V3 le = em.type == PRT_MAT_DEBUG ? em.kd : em.emission;
+                            const double pb = (double)(float)cosinePdf; /* carried as a float by the CUDA path record */
+                            const double d2 = dot(sd, sd);
+                            const double cosl = std::fabs(dot(peek.normal, sd)) / std::sqrt(d2);
+                            double pl = 0.0;
+                            if (peek.front && cosl > 0.0) pl = (1.0 / s.nodes[s.lights_root].area) * (peek.time * peek.time * d2) / cosl;
+                            scatter = att * le * (pb / (pb + pl)) / rr;
                         }
                     }
                 } else {

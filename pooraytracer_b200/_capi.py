@@ -35,6 +35,7 @@ RENDER_STAGE_TIMING = 4
 RENDER_PIXEL_JITTER = 8
 RENDER_UNBIASED_LIGHT_PICK = 16
 RENDER_LOBE_PROBABILITY = 32
+RENDER_MIS = 64
 
 LOAD_STRTOD = 1
 

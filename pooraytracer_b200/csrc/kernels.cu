@@ -384,6 +384,20 @@ struct ExtendPolicy {
                         const d3 le = mk3(m->emission[0], m->emission[1], m->emission[2]);
                         if (bounce == 0) L0 = le;
                         else st3(r->L, ld3(r->L) + ld3(r->T) * le);
+                    } else if ((rc.flags & PRT_RENDER_MIS) && r->prev_pdf > 0.f) {
+                        /* PRT_RENDER_MIS: the emitter the reference drops (Camera.cpp:187-196), weighted against the
+                         * light sampler's density for this point (0 if it shows its back). T already holds att / rr. */
+                        const TriShade* __restrict__ sh = S.shade + prim;
+                        const DevMaterial* m = S.materials + sh->material;
+                        const d3 le = mk3(m->emission[0], m->emission[1], m->emission[2]);
+                        const d3 dir = ld3(r->d), n = mk3(sh->normal[0], sh->normal[1], sh->normal[2]);
+                        const double pb = (double)r->prev_pdf;
+                        const double d2 = dot(dir, dir);
+                        const double dn = dot(dir, n);
+                        const double cosl = fabs(dn) / sqrt(d2);
+                        double pl = 0.0;
+                        if (dn < 0.0 && cosl > 0.0) pl = (1.0 / S.lights_area) * (h.t * h.t * d2) / cosl;
+                        st3(r->L, ld3(r->L) + ld3(r->T) * le * (pb / (pb + pl)));
                     }
                 } else if (c < CLS_SHADED) {
                     r->hit_prim = prim;
@@ -398,6 +412,7 @@ struct ExtendPolicy {
                         st3(r->T, mk3(1.0, 1.0, 1.0));
                         r->dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u;
                         r->flags = 0u;
+                        r->prev_pdf = 0.f;
                     }
                     cls = c;
                 }
@@ -539,7 +554,13 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
                     const d3 fr = material_eval(S, m, local_wi, wo, s.uv, rng);
                     const double cos_theta = local_wi.z;
                     const double cos_theta_bar = dot(local_ln, -local_wi);
-                    const d3 direct = emission * fr * cos_theta * cos_theta_bar / (distance * distance) / ls.pdf;
+                    d3 direct = emission * fr * cos_theta * cos_theta_bar / (distance * distance) / ls.pdf;
+                    if ((rc.flags & PRT_RENDER_MIS) && (CLS == CLS_LAMBERT || (CLS == CLS_PHONG && m.pkd == 1.0))) {
+                        /* balance heuristic against the cosine lobe's density for the same direction */
+                        const double pl = ls.pdf * (distance * distance) / cos_theta_bar;
+                        const double pb = cos_theta * PRT_INV_PI;
+                        direct = direct * (pl / (pl + pb));
+                    }
                     st3(r->sdir, light_dir);
                     r->sdist = distance;
                     st3(r->scontrib, T * direct);
@@ -551,8 +572,9 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
             if (rng.next() < rc.rr) {
                 d3 att, out_dir;
                 bool scattered = true;
-                if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, out_dir);
-                else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, out_dir, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
+                double cosine_pdf = 0.0;
+                if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, out_dir, cosine_pdf);
+                else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, out_dir, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
                 else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, out_dir);
                 else scatter_mirror(s, wo, att, out_dir);
                 /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
@@ -562,6 +584,7 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
                     st3(r->T, T * att / rc.rr);
                     r->dim = rng.dim;
                     r->flags = m.skip_light_sampling ? PRT_FLAG_PREV_SKIP : 0u;
+                    r->prev_pdf = (rc.flags & PRT_RENDER_MIS) ? (float)cosine_pdf : 0.f;
                     want_extend = true;
                     if (sort) key_extend = ray_key(rc.key_lo, rc.key_scale, s.position, out_dir);
                 }

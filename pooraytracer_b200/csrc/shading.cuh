@@ -164,9 +164,13 @@ __device__ __forceinline__ d3 material_eval(const DevScene& S, const DevMaterial
     return mk3(0, 0, 0);
 }
 
-__device__ __forceinline__ void scatter_lambertian(const DevScene& S, const DevMaterial& m, const Surface& s, Rng& rng, d3& att, d3& out_dir) {
+/* cosine_pdf (both scatter functions): the pdf of the sampled direction where it came from the cosine lobe, else 0
+ * (PRT_RENDER_MIS) */
+__device__ __forceinline__ void scatter_lambertian(const DevScene& S, const DevMaterial& m, const Surface& s, Rng& rng, d3& att, d3& out_dir,
+                                                   double& cosine_pdf) {
     const d3 wi = sample_cosine_hemisphere_upper(rng);
     const double pdf = wi.z * PRT_INV_PI;
+    cosine_pdf = pdf;
     const d3 f = tex_or_color(S, m.kd_tex, m.kd, s.uv) * PRT_INV_PI;
     out_dir = local_to_world(wi, s);
     att = f * wi.z / pdf;
@@ -174,7 +178,7 @@ __device__ __forceinline__ void scatter_lambertian(const DevScene& S, const DevM
 
 /* lobe_probability (PRT_RENDER_LOBE_PROBABILITY, never the parity default): divide by the probability of the sampled lobe */
 __device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMaterial& m, const Surface& s, d3 wo, Rng& rng, d3& att, d3& out_dir,
-                                              bool lobe_probability = false) {
+                                              double& cosine_pdf, bool lobe_probability = false) {
     d3 wi = mk3(0, 0, 0), f = mk3(0, 0, 0);
     double pdf = 0.0;
     const double u = rng.next();
@@ -203,6 +207,7 @@ __device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMateri
     att = mk3(0, 0, 0);
     if (pdf > 0. && wi.z > 0) att = f * wi.z / pdf;
     if (lobe_probability) att = att / (u < m.pkd ? m.pkd : m.pks);
+    cosine_pdf = (u < m.pkd && m.pkd == 1.0) ? pdf : 0.0;
 }
 
 __device__ __forceinline__ void scatter_mirror(const Surface& s, d3 wo, d3& att, d3& out_dir) {

@@ -321,13 +321,13 @@ def test_pixel_jitter_opt_in(gpu_ctx):
         del os.environ["PRT_TAIL_PATHS"]
 
 
-@pytest.mark.parametrize("name", ["tiny_nee", "veach_nee"])
+@pytest.mark.parametrize("name", ["tiny_nee", "veach_nee", "cornell_nee", "bathroom_nee"])
 def test_corrected_estimators_match_the_port(gpu_ctx, name):
-    """PRT_RENDER_UNBIASED_LIGHT_PICK | PRT_RENDER_LOBE_PROBABILITY | PRT_RENDER_PIXEL_JITTER (all off by
+    """PRT_RENDER_UNBIASED_LIGHT_PICK | PRT_RENDER_LOBE_PROBABILITY | PRT_RENDER_PIXEL_JITTER | PRT_RENDER_MIS (all off by
     default, none of them the reference's estimator): CUDA against the oracle port at the bar of the golden renders;
     what the switches do is tested on the port in the CPU suite."""
     sc, cam, prm = _render_case(name)
-    flags = capi.RENDER_UNBIASED_LIGHT_PICK | capi.RENDER_LOBE_PROBABILITY | capi.RENDER_PIXEL_JITTER
+    flags = capi.RENDER_UNBIASED_LIGHT_PICK | capi.RENDER_LOBE_PROBABILITY | capi.RENDER_PIXEL_JITTER | capi.RENDER_MIS
     p2 = make_params(prm.samples_per_pixel, prm.max_depth, rng_key=prm.rng_key, flags=flags)
     s = Scene(gpu_ctx, sc)
     O = ol.OracleScene("orc", sc, ol.DEFINE_UB)
@@ -335,6 +335,15 @@ def test_corrected_estimators_match_the_port(gpu_ctx, name):
     ref, _ = O.render(cam, p2)
     _compare_images(img, ref, name + " corrected vs port")
     assert not np.array_equal(img, s.render(cam, prm))
+    # MIS alone, and through per-bounce launches as well as the tail kernel
+    pm = make_params(prm.samples_per_pixel, prm.max_depth, rng_key=prm.rng_key, flags=capi.RENDER_MIS)
+    img_m = s.render(cam, pm)
+    _compare_images(img_m, O.render(cam, pm)[0], name + " MIS vs port")
+    os.environ["PRT_TAIL_PATHS"] = "0"
+    try:
+        assert np.array_equal(s.render(cam, pm), img_m)
+    finally:
+        del os.environ["PRT_TAIL_PATHS"]
 
 
 def test_resolve_matches_reference_quantiser(gpu_ctx):

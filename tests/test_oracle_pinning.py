@@ -205,3 +205,27 @@ def test_corrected_estimators_are_opt_in_and_do_what_they_claim():
         floor = img[..., 0] < 5  # not the light itself
         ratio[fl] = float(img[:, :16, 0][floor[:, :16]].mean() / img[:, 16:, 0][floor[:, 16:]].mean())
     assert ratio[0] > 1.2 and abs(ratio[capi.RENDER_UNBIASED_LIGHT_PICK] - 1.0) < 0.03, ratio
+
+
+def test_mis_is_opt_in_unbiased_and_lowers_variance():
+    """PRT_RENDER_MIS in the port (off by default): a quad light 0.3 above a floor, one bounce. With the
+    unbiased light pick on in both, light sampling alone and light + BSDF sampling under the balance heuristic estimate
+    the same direct lighting (means agree to 1 % over 8 x 64 spp; measured 0.04625 vs 0.04629), and MIS has the lower
+    per-pixel variance under a near light (measured -33 %)."""
+    from pooraytracer_b200 import _capi as capi
+    from pooraytracer_b200.scenes import _Builder, Material, quad
+    b = _Builder("near-light")
+    wh = b.material(Material("DiffuseWhite", capi.MAT_LAMBERTIAN, kd=(0.7, 0.7, 0.7)))
+    li = b.material(Material("Light", capi.MAT_DIFFUSE_LIGHT, emission=(10.0, 10.0, 10.0)))
+    b.mesh("floor", wh, *quad((-2, 0, 2), (2, 0, 2), (2, 0, -2), (-2, 0, -2)))
+    b.mesh("light", li, *quad((-1, 0.3, -0.2), (1, 0.3, -0.2), (1, 0.3, 0.2), (-1, 0.3, 0.2)))
+    sc = b.build(dict(width=32, height=16, fovy=60.0, eye=(0, 4, 0.001), look_at=(0, 0, 0), up=(0, 0, -1)))
+    O = ol.OracleScene("orc", sc, ol.DEFINE_UB)
+    cam = make_camera(sc.camera, 32, 16)
+    out = {}
+    for name, fl in (("nee", capi.RENDER_UNBIASED_LIGHT_PICK), ("mis", capi.RENDER_UNBIASED_LIGHT_PICK | capi.RENDER_MIS)):
+        st = np.stack([O.render(cam, make_params(64, 1, sample_lights=True, rr=1.0, rng_key=k, flags=fl))[0] for k in range(8)])
+        floor = st.mean(0)[..., 0] < 5
+        out[name] = (float(st[..., 0][:, floor].mean()), float(st[..., 0].var(axis=0)[floor].mean()))
+    assert abs(out["mis"][0] - out["nee"][0]) < 0.01 * out["nee"][0], out
+    assert out["mis"][1] < 0.85 * out["nee"][1], out
