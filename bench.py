@@ -58,7 +58,8 @@ def parse():
     ap.add_argument("--scene", default="cornell-box", choices=["cornell-box", "veach-mis", "bathroom2"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4", "lbvh", "bvh4q"])
-    ap.add_argument("--cpu-spp", type=int, default=1, help="spp of the bounded CPU sample")
+    ap.add_argument("--cpu-spp", type=int, default=0,
+                    help="spp of the bounded CPU sample (0 = 12 for the cpu_baseline of the b200 arm, about 13 s of 16 host cores on the default workload; 2 per step for --impl reference)")
     ap.add_argument("--max-leaf", type=int, default=0, help="triangles per BVH leaf (0 = the library's default, 4)")
     return ap.parse_args()
 
@@ -156,7 +157,7 @@ def run_reference(a):
     if rank != 0:
         return
     t0 = time.time()
-    v, info = cpu_reference_leg(a, a.cpu_spp, steps=max(1, a.steps), warmup=min(a.warmup, 1))
+    v, info = cpu_reference_leg(a, a.cpu_spp or 2, steps=max(1, a.steps), warmup=min(a.warmup, 1))
     line = {
         "impl": "reference", "metric": "spp_per_s", "value": v, "unit": "spp/s", "n_gpus": a.gpus, "steps": a.steps,
         "warmup": min(a.warmup, 1), "ms_per_step": info["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -322,7 +323,7 @@ def run_b200(a):
             "clocks": clk,
         }
         if not a.no_cpu_baseline and world == 1:
-            v, info = cpu_reference_leg(a, a.cpu_spp)
+            v, info = cpu_reference_leg(a, a.cpu_spp or 12)
             line["cpu_baseline"] = {"value": v, "unit": "spp/s", "cores": info["cores"], "kind": info["kind"], "sample": info["sample"],
                                     "mrays_s": info["mrays_s"]}
         print(json.dumps(line), flush=True)
