@@ -46,6 +46,9 @@ namespace prt {
 #ifndef PRT_EXTEND_DEFER
 #define PRT_EXTEND_DEFER 0
 #endif
+#ifndef PRT_BOUNCE0_LEAN
+#define PRT_BOUNCE0_LEAN 1 /* bounce 0: k_shade recomputes the camera ray and T = 1 instead of reading them back */
+#endif
 #define PRT_FLAG_PREV_SKIP 1u /* the vertex that scattered this ray skipped light sampling */
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
@@ -405,14 +408,16 @@ struct ExtendPolicy {
                     r->hit[1] = h.alpha;
                     r->hit[2] = h.beta;
                     if (bounce == 0) {
+                        r->dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u; /* same sector as the hit */
+#if !PRT_BOUNCE0_LEAN
                         d3 o, d;
                         camera_ray(rc, slot, o, d);
                         st3(r->o, o);
                         st3(r->d, d);
                         st3(r->T, mk3(1.0, 1.0, 1.0));
-                        r->dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u;
                         r->flags = 0u;
                         r->prev_pdf = 0.f;
+#endif
                     }
                     cls = c;
                 }
@@ -503,8 +508,11 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
         slot_next2 = (int64_t)qi + 2 * (int64_t)stride < n ? __ldcg(queue + qi + 2 * stride) : -1;
 #endif
 #if PRT_SHADE_PREFETCH && !PRT_SHADE_PIPE
-        if (slot_next >= 0) {
-            prefetch_l2(pb.rec + slot_next);
+#ifndef PRT_LEAN_PREFETCH0
+#define PRT_LEAN_PREFETCH0 1 /* 0: no prefetch at bounce 0 (the queue is in slot order there) */
+#endif
+        if (slot_next >= 0 && (PRT_LEAN_PREFETCH0 || !PRT_BOUNCE0_LEAN || bounce != 0)) {
+            prefetch_l2(PRT_BOUNCE0_LEAN && bounce == 0 ? (const void*)pb.rec[slot_next].hit : (const void*)(pb.rec + slot_next));
 #if PRT_SHADE_PREFETCH > 1
             prefetch_l2(reinterpret_cast<const char*>(pb.rec + slot_next) + 128);
 #endif
@@ -522,7 +530,15 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
             const DevMaterial m = S.materials[sh->material];
 #endif
             const double t = r->hit[0], alpha = r->hit[1], beta = r->hit[2];
+#if PRT_BOUNCE0_LEAN
+            /* bounce 0: the camera ray and T = 1 are recomputed here instead of being written by k_extend and
+             * read back (96 B less read here, 64 B less written there, per path: the two launches are DRAM-bound) */
+            d3 ro, rd;
+            if (bounce == 0) camera_ray(rc, slot, ro, rd);
+            else { ro = ld3(r->o); rd = ld3(r->d); }
+#else
             const d3 ro = ld3(r->o), rd = ld3(r->d);
+#endif
             /* the HitRecord of Triangle::Hit (Triangle.cpp:76-80,111) */
             Surface s;
             s.position = ro + rd * t;
@@ -536,7 +552,11 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
             Rng rng;
             rng.seed = stream_seed(rc.rng_key, (uint32_t)(slot % rc.npix), (uint32_t)(rc.sample_first + slot / rc.npix));
             rng.dim = r->dim;
+#if PRT_BOUNCE0_LEAN
+            const d3 T = bounce == 0 ? mk3(1.0, 1.0, 1.0) : ld3(r->T);
+#else
             const d3 T = ld3(r->T);
+#endif
 
             /* ---- next-event estimation (Camera.cpp:137-174) ---- */
             if (rc.sample_lights && !m.skip_light_sampling) {
