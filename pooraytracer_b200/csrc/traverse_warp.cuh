@@ -192,6 +192,19 @@ void trace_reference_cold(const DevScene& S, d3 o, d3 d, double tmin, double tma
 #ifndef PRT_TRAV_PREFETCH
 #define PRT_TRAV_PREFETCH 0
 #endif
+#ifndef PRT_PREFETCH_LEAF
+#define PRT_PREFETCH_LEAF 0      /* 1: L1, 2: L2 prefetch of a leaf's first triangle when the lane reaches it */
+#endif
+#ifndef PRT_PREFETCH_PUSH
+#define PRT_PREFETCH_PUSH 0      /* prefetch the second-nearest child (top of the stack) as it is pushed */
+#endif
+__device__ __forceinline__ void prefetch_line(const void* p) {
+#if PRT_PREFETCH_LEAF == 2 || PRT_PREFETCH_PUSH == 2
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+}
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 /*
@@ -471,8 +484,16 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                             if (s2 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s2); else overflow = true; }
                             if (s1 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s1); else overflow = true; }
                             cur = PRT_CHILD_OF(s0);
+#if PRT_PREFETCH_PUSH
+                            if (s1 != MISS && stack[sp - 1] >= 0) prefetch_line(WIDE == 40 ? (const void*)(S.nodes4q + stack[sp - 1]) : (const void*)(S.nodes4 + stack[sp - 1]));
+#endif
                         }
 #undef PRT_CHILD_OF
+#if PRT_PREFETCH_LEAF
+                        /* a lane that reached a leaf waits for the others to finish their inner nodes:
+                         * start pulling its first triangle in meanwhile */
+                        if (cur < 0) prefetch_line(S.tris + ((~cur) >> 3));
+#endif
                     } else {
 #if PRT_LD256
                         const char* __restrict__ p = reinterpret_cast<const char*>(S.nodes2 + cur);

@@ -1,0 +1,61 @@
+#!/usr/bin/env python3
+"""profiles/r1_traffic.json from an ncu launch list of bench.py.
+
+  python tools/traffic_from_launches.py <launches.csv> <name it is committed under> [workload accel spp]
+
+The list is the CSV of
+  ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none
+      python bench.py --steps 1 --warmup 1 --no-cpu-baseline
+which renders several identical steps (warm-up, timed, stage-timed, end-to-end); the number of steps is
+the number of k_tail<0, ...> launches (one per pass) and every figure is divided by it. The instrumented
+step (k_*<1, ...>, the counting build of the kernels) is left out; kernels it shares with the plain steps
+(k_shade, k_accumulate) are divided by one step more.
+"""
+import csv, json, re, sys
+from collections import defaultdict
+
+def main():
+    path, committed = sys.argv[1], sys.argv[2]
+    workload, accel, spp = (sys.argv[3:6] + ["cornell-box", "bvh4", "64"][len(sys.argv) - 3:])[:3]
+    rows = [r for r in csv.reader(l for l in open(path) if l.startswith('"'))]
+    head, rows = rows[0], rows[1:]
+    ik, im, iv, iid = head.index("Kernel Name"), head.index("Metric Name"), head.index("Metric Value"), head.index("ID")
+    per = defaultdict(lambda: defaultdict(float))
+    ids = defaultdict(set)
+    for r in rows:
+        m = re.search(r"prt::(k_\w+(?:<[^>]*>)?)", r[ik])
+        if not m:
+            continue
+        k = m.group(1).replace("(bool)", "").replace("(int)", "")
+        per[k][r[im]] += float(r[iv].replace(",", ""))
+        ids[k].add(r[iid])
+    steps = max(len(v) for k, v in ids.items() if k.startswith("k_tail<0"))
+    counted = max([len(v) for k, v in ids.items() if k.startswith("k_tail<1")] + [0])
+    out = {}
+    for k in sorted(per):
+        if re.match(r"k_\w+<1", k):
+            continue
+        # kernels without the COUNT template parameter (shade, accumulate) also ran in the instrumented step
+        n = steps if re.match(r"k_(extend|shadow|tail|trace)", k) else steps + counted
+        out[k] = {
+            "launches_per_step": len(ids[k]) / n,
+            "ms_per_step_under_ncu": per[k]["gpu__time_duration.sum"] / 1e6 / n,
+            "dram_bytes_per_step": (per[k]["dram__bytes_read.sum"] + per[k]["dram__bytes_write.sum"]) / n,
+        }
+    trav = [v for k, v in out.items() if k.startswith(("k_extend", "k_shadow"))]
+    tb = sum(v["dram_bytes_per_step"] for v in trav)
+    tl = sum(v["launches_per_step"] for v in trav)
+    j = {
+        "what": f"dram__bytes_read.sum + dram__bytes_write.sum per kernel, summed over the launches of ONE step "
+                f"({spp} spp of {workload}, {accel}), from {committed} (ncu --metrics gpu__time_duration.sum,"
+                f"dram__bytes_read.sum,dram__bytes_write.sum --clock-control none python bench.py --steps 1 --warmup 1 "
+                f"--no-cpu-baseline; {steps} identical steps in the list, figures divided by {steps})",
+        "workload": workload, "accel": accel, "spp_per_step": int(spp),
+        "traversal_dram_bytes_per_step": tb, "traversal_launches_per_step": tl,
+        "traversal_dram_bytes_per_launch": tb / tl if tl else None,
+        "kernels": out,
+    }
+    print(json.dumps(j, indent=1))
+
+if __name__ == "__main__":
+    main()
