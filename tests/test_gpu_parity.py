@@ -359,3 +359,60 @@ def test_resolve_matches_reference_quantiser(gpu_ctx):
     want = (np.clip(srgb, 0.0, 0.9999) * 255).astype(np.uint8)
     assert np.abs(rgb8.astype(int) - want.astype(int)).max() <= 1 and (rgb8 == want).mean() > 0.999
     assert rgb8.max() <= 254 and np.array_equal(f32, lin.astype(np.float32))
+
+
+def test_full_size_render_properties(gpu_ctx, monkeypatch):
+    """BASELINE configs[1] at its own size (cornell-box 1024x1024, depth 100, NEE, RR 0.8), 4 of the 3000
+    samples: the properties that do not need a CPU render of the frame. The image is a function of
+    (scene, camera, sample range, RNG key) alone — not of the acceleration structure, the pass size, the
+    tail hand-over or the sample sharding — and the shards add up to the whole."""
+    sc = scenes.cornell_box(1024, 1024)
+    cam = make_camera(sc.camera, 1024, 1024)
+
+    def prm(b, e):
+        return make_params(3000, 100, rr=0.8, rng_key=20251104, spp_begin=b, spp_end=e)
+
+    s4 = Scene(gpu_ctx, sc, accel=capi.ACCEL_SAH_BVH4)
+    base = s4.render(cam, prm(0, 4))
+    st = s4.stats()
+    assert base.shape == (1024, 1024, 3) and np.isfinite(base).all() and (base >= 0).all()
+    assert st.extend_rays >= 4 * 1024 * 1024 and st.shadow_rays > 0
+    # the light is visible and the walls are lit: not a black or a saturated frame
+    lum = base.sum(axis=-1)
+    assert (lum > 0).mean() > 0.5
+    for accel in (capi.ACCEL_SAH_BVH2, capi.ACCEL_LBVH4_DEVICE, capi.ACCEL_SAH_BVH4Q, capi.ACCEL_REFERENCE_BVH2):
+        other = Scene(gpu_ctx, sc, accel=accel).render(cam, prm(0, 4))
+        assert np.array_equal(other, base), f"accel {accel} changes the full-size image"
+    monkeypatch.setenv("PRT_PASS_PATHS", str(1 << 20))  # four passes instead of one
+    assert np.array_equal(s4.render(cam, prm(0, 4)), base)
+    monkeypatch.delenv("PRT_PASS_PATHS")
+    monkeypatch.setenv("PRT_TAIL_PATHS", "0")  # per-bounce launches to the end
+    assert np.array_equal(s4.render(cam, prm(0, 4)), base)
+    monkeypatch.delenv("PRT_TAIL_PATHS")
+    # sample sharding as the multi-GPU path does it: the shards carry the 1/spp weight already
+    parts = s4.render(cam, prm(0, 1)) + s4.render(cam, prm(1, 4))
+    assert np.allclose(parts, base, rtol=1e-13, atol=1e-15)
+
+
+def test_full_size_ray_query_properties(gpu_ctx):
+    """BASELINE configs[4] at 1 M triangles (terrain 1000x500 quads), 2^22 random rays: closest hits do not
+    depend on the acceleration structure (bit-exact), and any-hit agrees with closest-hit on both sides
+    of the hit distance."""
+    sc = scenes.terrain(1000, 500)
+    o, d = scenes.random_rays(sc, 1 << 22)
+    ref = None
+    for accel in (capi.ACCEL_SAH_BVH4, capi.ACCEL_SAH_BVH2, capi.ACCEL_LBVH4_DEVICE, capi.ACCEL_SAH_BVH4Q):
+        s = Scene(gpu_ctx, sc, accel=accel)
+        got = s.trace_closest(o, d, 1e-4, np.inf)
+        if ref is None:
+            ref, s_ref = got, s
+        else:
+            for a, b in zip(got, ref):
+                assert np.array_equal(a, b, equal_nan=True), f"accel {accel}"
+    prim, t = ref[0], ref[1]
+    hit = prim >= 0
+    assert 0.05 < hit.mean() < 0.95
+    tmax = np.where(hit, t * (1 + 1e-9), 1e30)
+    assert np.array_equal(s_ref.trace_any(o, d, 1e-4, tmax).astype(bool), hit)
+    tshort = np.where(hit, t * (1 - 1e-9), 1e30)
+    assert not s_ref.trace_any(o, d, 1e-4, tshort).astype(bool).any()
