@@ -24,6 +24,12 @@ def split_samples(total_spp: int, rank: int, world: int) -> tuple[int, int]:
     return begin, begin + base + (1 if rank < extra else 0)
 
 
+def ray_range(n_rays: int, rank: int, world: int) -> tuple[int, int]:
+    """Ray queries (SURVEY 8e): the r-th of `world` contiguous, balanced ranges of a batch of `n_rays`;
+    no collective, every rank returns the results of its own range."""
+    return split_samples(n_rays, rank, world)
+
+
 def reduce_image(acc, dst: int = 0):
     """The single collective: sum of the accumulators on rank `dst` (NCCL over NVLink on GPUs, gloo in
     the CPU tests). `acc` is a torch tensor; no-op when torch.distributed is not initialised."""

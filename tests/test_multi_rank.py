@@ -73,3 +73,52 @@ def test_sample_ranges_partition():
                 seen.append(sample_range(step, 16, r, world))
         flat = sorted(seen)
         assert flat[0][0] == 0 and all(flat[i][1] == flat[i + 1][0] for i in range(len(flat) - 1))
+
+
+def _ray_worker(rank, world, port, out_path):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import cases
+    import oracle_lib as ol
+    from pooraytracer_b200.sharding import ray_range
+    sc = cases.tiny()
+    o, d = cases.ray_batch(sc)
+    n = (o.shape[0] // 2) * 2 - 1  # odd: the two ranges differ in size
+    o, d = o[:n], d[:n]
+    O = ol.OracleScene("orc", sc, 0)
+    b, e = ray_range(n, rank, world)
+    prim, t, al, be = O.trace_closest(o[b:e], d[b:e], 1e-4, np.inf, nthreads=1)
+    # no collective on the data path: every rank hands back its own range (here: gathered for the check)
+    mine = torch.full((n, 2), -7.0, dtype=torch.float64)
+    mine[b:e, 0] = torch.from_numpy(prim.astype(np.float64))
+    mine[b:e, 1] = torch.from_numpy(np.where(np.isfinite(t), t, -1.0))
+    parts = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
+    dist.gather(mine, parts, dst=0)
+    if rank == 0:
+        full = O.trace_closest(o, d, 1e-4, np.inf, nthreads=1)
+        got = torch.full((n, 2), -7.0, dtype=torch.float64)
+        for r, p in enumerate(parts):
+            rb, re_ = ray_range(n, r, world)
+            got[rb:re_] = p[rb:re_]
+        np.savez(out_path, got=got.numpy(), prim=full[0], t=np.where(np.isfinite(full[1]), full[1], -1.0))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_ranks_shard_a_ray_batch(built, tmp_path):
+    """Ray queries over N ranks: contiguous, balanced ranges whose union is the batch, each ray's answer
+    independent of the range it was traced in (bit-exact against the single-rank trace)."""
+    from pooraytracer_b200.sharding import ray_range
+    for world in (1, 2, 3, 8):
+        got = [ray_range(1 << 24, r, world) for r in range(world)]
+        assert got[0][0] == 0 and got[-1][1] == 1 << 24 and all(got[i][1] == got[i + 1][0] for i in range(world - 1))
+    out = str(tmp_path / "rays.npz")
+    port = 31500 + (os.getpid() % 2000)
+    mp.spawn(_ray_worker, args=(2, port, out), nprocs=2, join=True)
+    r = np.load(out)
+    assert np.array_equal(r["got"][:, 0], r["prim"].astype(np.float64))
+    assert np.array_equal(r["got"][:, 1], r["t"])
+    assert (r["prim"] >= 0).any()

@@ -4,6 +4,11 @@
 CUDA-event timing inside the library (prt_stats.gpu_ms). One JSON line per case.
 
   python tools/rayquery_bench.py --tris 1 --rays 24 [--mesh terrain|soup] [--check N]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/rayquery_bench.py ...
+
+Under torchrun the scene is replicated, rank r traces the r-th contiguous range of the batch
+(pooraytracer_b200/sharding.py:ray_range), there is no collective on the data path, and rank 0 prints the
+aggregate rate = all rays / the slowest rank's device time, with the per-GPU rates beside it.
 """
 import argparse
 import json
@@ -30,13 +35,21 @@ def main():
     import torch
     from pooraytracer_b200 import Context, Scene, _capi as capi, scenes
 
-    n = 1 << a.rays
+    rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    if world > 1:
+        import torch.distributed as dist
+        from pooraytracer_b200.sharding import ray_range
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_all = 1 << a.rays
+    lo_, hi_ = ray_range(n_all, rank, world) if world > 1 else (0, n_all)
+    n = hi_ - lo_
     if a.mesh == "terrain":
         sc = scenes.terrain(1000, 500) if a.tris == 1 else scenes.terrain(2500, 2000)
     else:
         sc = scenes.soup(a.tris * 1_000_000)
     t0 = time.time()
-    ctx = Context(0)
+    ctx = Context(local)
     scene = Scene(ctx, sc, accel=None)
     t_create = time.time() - t0
     t0 = time.time()
@@ -52,10 +65,11 @@ def main():
     diag = float(np.linalg.norm(sc.vertices.reshape(-1, 3).max(0) - sc.vertices.reshape(-1, 3).min(0)))
     for kind in ("random", "coherent"):
         if kind == "random":
-            o, d = scenes.random_rays(sc, n)
+            o, d = scenes.random_rays(sc, n_all)
         else:
             side = 1 << (a.rays // 2)
-            o, d = scenes.camera_rays(sc.camera, side, n // side)
+            o, d = scenes.camera_rays(sc.camera, side, n_all // side)
+        o, d = np.ascontiguousarray(o[lo_:hi_]), np.ascontiguousarray(d[lo_:hi_])
         do, dd = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
         tmin = torch.full((n,), 1e-4, dtype=torch.float64, device="cuda")
         tmax = torch.full((n,), float("inf"), dtype=torch.float64, device="cuda")
@@ -63,7 +77,7 @@ def main():
         t = torch.empty(n, dtype=torch.float64, device="cuda")
         al, be = torch.empty_like(t), torch.empty_like(t)
         hit = torch.empty(n, dtype=torch.uint8, device="cuda")
-        tmax_any = torch.from_numpy(scenes.hash_uniform(n, 5, 1) * diag).cuda()
+        tmax_any = torch.from_numpy(np.ascontiguousarray((scenes.hash_uniform(n_all, 5, 1) * diag)[lo_:hi_])).cuda()
         tmin_any = torch.full((n,), 1e-3, dtype=torch.float64, device="cuda")
         torch.cuda.synchronize()
         for query in ("closest", "any"):
@@ -82,12 +96,26 @@ def main():
             scene.set_counters(False)
             run()
             ms = min(run().gpu_ms for _ in range(a.reps))
+            hits = float((prim >= 0).float().sum().item()) if query == "closest" else float(hit.float().sum().item())
+            per_gpu = None
+            if world > 1:
+                # aggregate = all rays / the slowest rank; counters and hits summed over the ranks
+                v = torch.tensor([ms, float(nodes), float(tris), hits, float(n)], dtype=torch.float64, device="cuda")
+                g = [torch.empty_like(v) for _ in range(world)]
+                dist.all_gather(g, v)
+                g = torch.stack(g).cpu().numpy()
+                per_gpu = [float(r[4] / r[0] / 1e3) for r in g]
+                ms, nodes, tris, hits, n_tot = float(g[:, 0].max()), int(g[:, 1].sum()), int(g[:, 2].sum()), float(g[:, 3].sum()), int(g[:, 4].sum())
+                if rank != 0:
+                    continue
+            else:
+                n_tot = n
             alg = nodes * st.node_bytes + tris * st.tri_bytes
-            line = {"case": f"{a.mesh}-{sc.n_triangles} {kind} {query}", "rays": n, "mrays_s": n / ms / 1e3, "ms": ms,
-                    "nodes_per_ray": nodes / n, "tris_per_ray": tris / n, "bytes_per_ray": alg / n,
-                    "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                                 "frac": alg / (ms * 1e-3) / 1e9 / peak},
-                    "hit_fraction": float((prim >= 0).float().mean().item()) if query == "closest" else float(hit.float().mean().item()),
+            line = {"case": f"{a.mesh}-{sc.n_triangles} {kind} {query}", "n_gpus": world, "rays": n_tot, "mrays_s": n_tot / ms / 1e3, "ms": ms,
+                    "nodes_per_ray": nodes / n_tot, "tris_per_ray": tris / n_tot, "bytes_per_ray": alg / n_tot,
+                    "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s",
+                                 "frac": alg / (ms * 1e-3) / 1e9 / (peak * world)},
+                    "hit_fraction": hits / n_tot,
                     "scene_create_s": t_create, "scene_commit_s": t_commit, "n_nodes": st.n_nodes, "build_ms": st.build_ms}
             if a.check and query == "closest" and kind == "random":
                 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -97,7 +125,12 @@ def main():
                 want = O.trace_closest(o[:m], d[:m], 1e-4, np.inf, nthreads=os.cpu_count() or 4)
                 got = (prim[:m].cpu().numpy(), t[:m].cpu().numpy(), al[:m].cpu().numpy(), be[:m].cpu().numpy())
                 line["oracle_check"] = {"rays": m, "bit_exact": bool(all(np.array_equal(x, y) for x, y in zip(got, want)))}
+            if per_gpu:
+                line["mrays_s_per_gpu"] = per_gpu
             print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
