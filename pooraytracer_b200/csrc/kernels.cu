@@ -179,6 +179,7 @@ __global__ void __launch_bounds__(256) k_query_keys(int64_t n, const double* __r
  * ray queries
  * ---------------------------------------------------------------------------------------------- */
 struct ClosestQueryPolicy {
+    static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_QUERY;
     const double *o, *d, *tmin, *tmax;
     int32_t* prim;
     double *t, *alpha, *beta;
@@ -206,6 +207,7 @@ struct ClosestQueryPolicy {
     __device__ __forceinline__ void finish() const {}
 };
 struct AnyQueryPolicy {
+    static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_QUERY;
     const double *o, *d, *tmin, *tmax;
     uint8_t* hit;
     const int32_t* __restrict__ order;
@@ -336,6 +338,7 @@ struct DeferredPush {
  * traverse_warp.cuh), then the terminal cases that need no BSDF, then one queue per material class
  * for the shade kernels. Bounce 0 generates its camera rays itself (no ray-generation pass). */
 struct ExtendPolicy {
+    static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_RENDER;
     const DevScene& S;
     const uint8_t* __restrict__ prim_class;
     const RenderConst& rc;
@@ -662,6 +665,7 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
  * query over [1e-3, distance - 1e-3]. PRT_RENDER_EXACT_VISIBILITY runs the literal test instead. */
 template <bool EXACT>
 struct ShadowPolicy {
+    static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_RENDER;
     const PathBuffers& pb;
     const int32_t* queue;
     d3 ps, dir;

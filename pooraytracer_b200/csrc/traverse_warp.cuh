@@ -47,8 +47,22 @@ namespace prt {
 #define PRT_SAH_STACK 64         /* entries of the SAH / LBVH walk's stack; a ray that overflows it is handed to the
                                     reference-order walk (whose own depth is bounded by log2 of the mesh sizes) */
 #endif
-#ifndef PRT_REFILL_BELOW
-#define PRT_REFILL_BELOW 16      /* refill idle lanes once fewer than this many lanes hold a ray */
+/* refill idle lanes once fewer than this many lanes hold a ray (Policy::REFILL_BELOW). Refilling early keeps
+ * lanes busy; refilling late keeps the rays of a warp (and the path vertices they push for k_shade) together.
+ * Measured (profiles/r1_s8_ab.txt): the render kernels like 12, 2^24-ray query batches 20 */
+#ifndef PRT_REFILL_BELOW_RENDER
+#ifdef PRT_REFILL_BELOW
+#define PRT_REFILL_BELOW_RENDER PRT_REFILL_BELOW
+#else
+#define PRT_REFILL_BELOW_RENDER 12
+#endif
+#endif
+#ifndef PRT_REFILL_BELOW_QUERY
+#ifdef PRT_REFILL_BELOW
+#define PRT_REFILL_BELOW_QUERY PRT_REFILL_BELOW
+#else
+#define PRT_REFILL_BELOW_QUERY 20
+#endif
 #endif
 
 /* PRT_BOX_AXIS_ERR = 1 (default): the origin error of each axis is folded into that axis alone.
@@ -420,7 +434,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
             }
             const unsigned walking = __ballot_sync(FULL, has_ray && !(cur == PRT_DONE && leaf < 0));
             if (walking == 0) break;
-            if (!exhausted && __popc(walking) < PRT_REFILL_BELOW) break;
+            if (!exhausted && __popc(walking) < P::REFILL_BELOW) break;
         }
         if (!ANY && has_ray && cur == PRT_DONE && leaf < 0 && hit.slot >= 0 && on_boundary(hit.alpha, hit.beta)) recheck = true;
 #else
@@ -553,7 +567,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
             if (cur == PRT_DONE && has_ray && !ANY && hit.slot >= 0 && on_boundary(hit.alpha, hit.beta)) recheck = true;
             const unsigned walking = __ballot_sync(FULL, has_ray && cur != PRT_DONE);
             if (walking == 0) break;
-            if (!exhausted && __popc(walking) < PRT_REFILL_BELOW) break;
+            if (!exhausted && __popc(walking) < P::REFILL_BELOW) break;
         }
 #endif
     }

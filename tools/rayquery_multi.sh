@@ -1,0 +1,15 @@
+# usage (on an N-GPU box): bash tools/rayquery_multi.sh N  -> gpurun_out/rq_nN.jsonl
+# BASELINE configs[4] over N GPUs: every rank holds the mesh and traces its contiguous range of the 2^24 rays.
+N=$1; : > gpurun_out/rq_n$N.jsonl
+p=29600
+for spec in "1 terrain" "1 soup" "10 terrain" "10 soup"; do
+  set -- $spec; p=$((p+1))
+  timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $p \
+    tools/rayquery_bench.py --tris $1 --rays 24 --mesh $2 2> gpurun_out/rq_n${N}_$1_$2.err | grep '^{' >> gpurun_out/rq_n$N.jsonl
+  echo "$spec rc=$?"
+done
+python - gpurun_out/rq_n$N.jsonl <<'PY'
+import json,sys
+for l in open(sys.argv[1]):
+    j=json.loads(l); print(j['case'], 'n', j['n_gpus'], round(j['mrays_s']), 'Mrays/s  per GPU', [round(x) for x in j.get('mrays_s_per_gpu', [])])
+PY
