@@ -49,7 +49,9 @@ namespace prt {
 #endif
 /* refill idle lanes once fewer than this many lanes hold a ray (Policy::REFILL_BELOW). Refilling early keeps
  * lanes busy; refilling late keeps the rays of a warp (and the path vertices they push for k_shade) together.
- * Measured (profiles/r1_s8_ab.txt): the render kernels like 12, 2^24-ray query batches 20 */
+ * Measured (profiles/r1_s8_ab.txt): the render kernels like 8-12 (k_shade reads the records of consecutive
+ * queue entries: 35.2 -> 34.3 ms at 12, more than k_extend loses); for query batches 20 trades +4 % on random
+ * rays for -4 % on coherent ones, so they stay at 16 */
 #ifndef PRT_REFILL_BELOW_RENDER
 #ifdef PRT_REFILL_BELOW
 #define PRT_REFILL_BELOW_RENDER PRT_REFILL_BELOW
@@ -61,7 +63,7 @@ namespace prt {
 #ifdef PRT_REFILL_BELOW
 #define PRT_REFILL_BELOW_QUERY PRT_REFILL_BELOW
 #else
-#define PRT_REFILL_BELOW_QUERY 20
+#define PRT_REFILL_BELOW_QUERY 16
 #endif
 #endif
 
