@@ -665,7 +665,7 @@ __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S,
  * query over [1e-3, distance - 1e-3]. PRT_RENDER_EXACT_VISIBILITY runs the literal test instead. */
 template <bool EXACT>
 struct ShadowPolicy {
-    static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_RENDER;
+    static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_SHADOW;
     const PathBuffers& pb;
     const int32_t* queue;
     d3 ps, dir;

@@ -59,6 +59,9 @@ namespace prt {
 #define PRT_REFILL_BELOW_RENDER 12
 #endif
 #endif
+#ifndef PRT_REFILL_BELOW_SHADOW /* k_shadow pushes nothing: only its own lane occupancy counts */
+#define PRT_REFILL_BELOW_SHADOW PRT_REFILL_BELOW_RENDER
+#endif
 #ifndef PRT_REFILL_BELOW_QUERY
 #ifdef PRT_REFILL_BELOW
 #define PRT_REFILL_BELOW_QUERY PRT_REFILL_BELOW
