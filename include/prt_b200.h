@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define PRT_ABI_VERSION 1
+#define PRT_ABI_VERSION 2
 
 /* ---- status codes ---------------------------------------------------------------------------- */
 #define PRT_OK 0
@@ -192,6 +192,10 @@ typedef struct prt_stats {
     int64_t  n_triangles;
     double   build_ms;         /* PRT_ACCEL_LBVH4_DEVICE: device time of the BVH build (CUDA events);
                                   0 for the host-built structures                                */
+    uint64_t ref_stack_overflows; /* STICKY error counter since commit: subtrees the reference-order walk (boundary /
+                                  equal-t re-trace, PRT_ACCEL_REFERENCE_BVH2) had to drop because its stack was full.
+                                  0 in a healthy build: its depth is log2(mesh size) + the top level. Non-zero means
+                                  results of those rays are not the reference's                   */
 } prt_stats;
 
 /* ---- lifecycle -------------------------------------------------------------------------------- */

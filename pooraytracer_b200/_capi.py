@@ -129,6 +129,7 @@ class PrtStats(C.Structure):
         ("n_nodes", C.c_int64),
         ("n_triangles", C.c_int64),
         ("build_ms", C.c_double),
+        ("ref_stack_overflows", C.c_uint64),
     ]
 
 
@@ -185,7 +186,7 @@ def load_library(path: str | None = None) -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError = symbol missing = broken build
         fn.restype = res
         fn.argtypes = args
-    if lib.prt_abi_version() != 1:
+    if lib.prt_abi_version() != 2:
         raise RuntimeError("pooraytracer_b200: ABI version mismatch")
     if path is None:
         _lib = lib

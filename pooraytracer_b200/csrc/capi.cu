@@ -110,12 +110,15 @@ struct prt_scene {
     DevBuf<uint8_t> s_hit;
     DevBuf<int32_t> d_fetch;             /* work cursor of the ray-query kernels */
     DevBuf<unsigned long long> d_counters; /* [2] node visits, triangle tests */
+    DevBuf<unsigned long long> d_err;      /* [1] sticky: subtrees dropped by the reference-order walk (DevScene::ref_overflow) */
     DevBuf<double> s_rgb;
     DevBuf<uint8_t> s_rgb8;
     DevBuf<float> s_rgb32f;
 
     /* wavefront pool */
     DevBuf<PathRec> p_rec;
+    DevBuf<PathL> p_lum;
+    DevBuf<PrimaryHit> p_primary;
     DevBuf<int32_t> p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qm3, p_qs;
     DevBuf<BounceCtrl> p_ctrl;
     /* ray binning (launch.h): keys, reordered queues, histograms + cursors; also used by the ray queries */
@@ -179,10 +182,13 @@ int64_t pass_path_budget() {
     const char* env = std::getenv("PRT_PASS_PATHS");
     int64_t v = env ? std::atoll(env) : (int64_t(1) << 26); /* 12.9 GB of path records: per-pass fixed costs (tail, drains) amortised over 4x the paths of 2^24, +9 % */
     if (v < 1024) v = 1024;
+    const int64_t top = (int64_t(1) << 31) - 64 - 4096; /* slots and queue positions are int32 (rounded up to whole warps) */
+    if (v > top) v = top;
     return v;
 }
 
-int ensure_pool(prt_scene* s, int64_t cap, int n_bounces, bool binning) {
+int ensure_pool(prt_scene* s, int64_t cap, int64_t npix, int n_bounces, bool binning) {
+    if ((int64_t)s->p_primary.n < npix) CUDA_TRY(s->p_primary.ensure((size_t)npix));
     if (binning && (int64_t)s->p_ke.n < cap) { /* ray-binning scratch only when PRT_SORT_MIN asks for it */
         CUDA_TRY(s->p_ke.ensure((size_t)cap));
         CUDA_TRY(s->p_ks.ensure((size_t)cap));
@@ -191,6 +197,7 @@ int ensure_pool(prt_scene* s, int64_t cap, int n_bounces, bool binning) {
     }
     if (cap > s->pool_cap) {
         CUDA_TRY(s->p_rec.ensure((size_t)cap));
+        CUDA_TRY(s->p_lum.ensure((size_t)cap));
         CUDA_TRY(s->p_q0.ensure((size_t)cap));
         CUDA_TRY(s->p_q1.ensure((size_t)cap));
         CUDA_TRY(s->p_qm0.ensure((size_t)cap));
@@ -211,6 +218,8 @@ PathBuffers path_buffers(prt_scene* s) {
     PathBuffers pb;
     pb.cap = s->pool_cap;
     pb.rec = s->p_rec.p;
+    pb.lum = s->p_lum.p;
+    pb.primary = s->p_primary.p;
     pb.q_extend[0] = s->p_q0.p; pb.q_extend[1] = s->p_q1.p;
     pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p; pb.q_mat[3] = s->p_qm3.p;
     pb.q_shadow = s->p_qs.p;
@@ -440,6 +449,8 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     CUDA_TRY(s->d_fetch.ensure(4));
     CUDA_TRY(s->d_counters.ensure(8));
     CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 8 * sizeof(unsigned long long), st));
+    CUDA_TRY(s->d_err.ensure(1));
+    CUDA_TRY(cudaMemsetAsync(s->d_err.p, 0, sizeof(unsigned long long), st));
     if (int e = ensure_sort_scratch(s, st)) return e;
     CUDA_TRY(cudaStreamSynchronize(st));
     DevScene& D = s->dev;
@@ -464,6 +475,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     D.srgb_lut = s->d_srgb.p;
     D.n_materials = (int32_t)h.dev_materials.size();
     D.n_textures = (int32_t)h.dev_textures.size();
+    D.ref_overflow = s->d_err.p;
     if (!s->ev0) {
         CUDA_TRY(cudaEventCreate(&s->ev0));
         CUDA_TRY(cudaEventCreate(&s->ev1));
@@ -643,6 +655,12 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     rcn.sample_lights = params->sample_lights ? 1 : 0;
     rcn.has_cook = s->has_cook ? 1 : 0;
     rcn.class_mask = s->class_mask;
+    /* primary-hit reuse (launch.h: PrimaryHit): valid whenever every sample of a pixel starts with the same ray, i.e.
+     * always for the reference's Camera::GetRay; PRT_PRIMARY_REUSE=0 keeps the per-sample bounce 0 (A/B, tests) */
+    {
+        const char* env = std::getenv("PRT_PRIMARY_REUSE");
+        rcn.primary_reuse = (params->flags & PRT_RENDER_PIXEL_JITTER) || (env && std::atoi(env) == 0) ? 0 : 1;
+    }
     rcn.flags = params->flags | (s->count_visits ? PRT_RENDER_COUNTERS : 0u);
     rcn.rr = params->russian_roulette;
     rcn.scale = 1.0 / params->samples_per_pixel;
@@ -654,7 +672,7 @@ int prt_render_device(prt_scene* s, const prt_camera* camera, const prt_render_p
     int per_pass = (int)std::max<int64_t>(1, budget / rcn.npix);
     per_pass = std::min(per_pass, std::max(1, se - sb));
     const int n_bounces = params->max_depth + 1;
-    rc = ensure_pool(s, (int64_t)per_pass * rcn.npix, n_bounces, launch_config(s->ctx).sort_min > 0);
+    rc = ensure_pool(s, (int64_t)per_pass * rcn.npix, rcn.npix, n_bounces, launch_config(s->ctx).sort_min > 0);
     if (rc) return rc;
     const bool counting = (rcn.flags & PRT_RENDER_COUNTERS) != 0;
     CUDA_TRY(cudaMemsetAsync(s->d_counters.p, 0, 8 * sizeof(unsigned long long), st));
@@ -775,6 +793,10 @@ int prt_get_stats(const prt_scene* cs, prt_stats* out) {
                 if (s->rays_pending) { s->stats.extend_rays = c[2]; s->stats.shadow_rays = c[3]; }
             }
             s->rays_pending = s->visits_pending = false;
+        }
+        if (s->d_err.p) {
+            unsigned long long e = 0;
+            if (cudaMemcpy(&e, s->d_err.p, sizeof(e), cudaMemcpyDeviceToHost) == cudaSuccess) s->stats.ref_stack_overflows = e;
         }
     }
     *out = s->stats;

@@ -137,6 +137,8 @@ struct DevScene {
     const uint8_t* texels;
     const double* srgb_lut; /* [256] SRGBToLinear(i/255) computed on the host (Texture.cpp:66-71) */
     int32_t n_materials, n_textures;
+    unsigned long long* ref_overflow; /* sticky error counter: subtrees the reference-order walk dropped because its
+                                         PRT_STACK-entry stack was full (prt_stats.ref_stack_overflows; 0 in a healthy build) */
 };
 
 }  // namespace prt

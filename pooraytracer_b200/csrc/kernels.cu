@@ -25,7 +25,9 @@
 #include <float.h>
 
 #include <algorithm>
-#include <unordered_map>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "../../include/prt_b200.h"
 #include "launch.h"
@@ -46,10 +48,7 @@ namespace prt {
 #ifndef PRT_EXTEND_DEFER
 #define PRT_EXTEND_DEFER 0
 #endif
-#ifndef PRT_BOUNCE0_LEAN
-#define PRT_BOUNCE0_LEAN 1 /* bounce 0: k_shade recomputes the camera ray and T = 1 instead of reading them back */
-#endif
-#define PRT_FLAG_PREV_SKIP 1u /* the vertex that scattered this ray skipped light sampling */
+/* PathRec::dimflags bit 31: the vertex that scattered this ray skipped light sampling (Camera.cpp:191-195) */
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
@@ -234,9 +233,10 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(
                                                        const double* __restrict__ tmin, const double* __restrict__ tmax,
                                                        int32_t* __restrict__ prim, double* __restrict__ t, double* __restrict__ alpha,
                                                        double* __restrict__ beta, const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
+    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     VisitCounters cnt = {0, 0, 0, 0, 0};
     ClosestQueryPolicy pol = {o, d, tmin, tmax, prim, t, alpha, beta, S.slot_prim, order};
-    traverse_persistent<false, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
+    traverse_persistent<false, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt, sm_stack);
     flush_counters<COUNT>(cnt, counters);
 }
 
@@ -244,9 +244,10 @@ template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                    const double* __restrict__ tmin, const double* __restrict__ tmax, uint8_t* __restrict__ hit,
                                                    const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
+    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     VisitCounters cnt = {0, 0, 0, 0, 0};
     AnyQueryPolicy pol = {o, d, tmin, tmax, hit, order};
-    traverse_persistent<true, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt);
+    traverse_persistent<true, COUNT, WIDE>(S, pol, fetch, (int32_t)n, cnt, sm_stack);
     flush_counters<COUNT>(cnt, counters);
 }
 
@@ -271,6 +272,13 @@ __device__ __forceinline__ d3 ld3(const double* p) { return mk3(p[0], p[1], p[2]
 __device__ __forceinline__ void st3(double* p, d3 v) {
     p[0] = v.x; p[1] = v.y; p[2] = v.z;
 }
+/* sector k of a path record / the radiance cell of a slot (launch.h) */
+__device__ __forceinline__ char* rec_sector(const PathBuffers& pb, int32_t slot, int k) { return reinterpret_cast<char*>(pb.rec + slot) + 32 * k; }
+__device__ __forceinline__ void lum_add(const PathBuffers& pb, int32_t slot, d3 v) {
+    const dd4 l = ld256g(pb.lum + slot);
+    st256g(pb.lum + slot, l.v[0] + v.x, l.v[1] + v.y, l.v[2] + v.z, 0.0);
+}
+__device__ __forceinline__ void lum_set(const PathBuffers& pb, int32_t slot, d3 v) { st256g(pb.lum + slot, v.x, v.y, v.z, 0.0); }
 
 /* Camera::GetRay (Camera.cpp:108-117): pixel centre, direction not normalised. slot = sample * npix + pixel */
 __device__ __forceinline__ void camera_ray(const RenderConst& rc, int32_t slot, d3& o, d3& d) {
@@ -334,9 +342,83 @@ struct DeferredPush {
     }
 };
 
+/* What a ray that ends its path at this hit leaves behind, without any BSDF (Camera.cpp:125-132,187-196).
+ * Returns the material class of the hit (CLS_SHADED.. = the path ends here) and, for a path that ends, the
+ * radiance `le` it collects BEFORE weighting (background / emission / 0). */
+__device__ __forceinline__ int terminal_radiance(const DevScene& S, const uint8_t* __restrict__ prim_class, const RenderConst& rc, const Hit& h,
+                                                 int32_t& prim, d3& le) {
+    le = mk3(0.0, 0.0, 0.0);
+    prim = -1;
+    if (h.slot < 0) {
+        le = mk3(rc.background[0], rc.background[1], rc.background[2]);
+        return CLS_EMPTY;
+    }
+    prim = S.slot_prim[h.slot];
+    const int c = prim_class[prim];
+    if (c == CLS_EMISSIVE) {
+        const DevMaterial* m = S.materials + S.shade[prim].material;
+        le = mk3(m->emission[0], m->emission[1], m->emission[2]);
+    }
+    return c;
+}
+
+/* Bounce 0, once per PIXEL (PrimaryHit, launch.h): the closest hit of the camera ray through the pixel centre,
+ * shared by every sample of the pixel. Pixels whose path goes on are queued per material class; k_shade<CLS, true>
+ * expands each queued pixel into its n_samples path slots. */
+struct PrimaryPolicy {
+    static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_QUERY;
+    const DevScene& S;
+    const uint8_t* __restrict__ prim_class;
+    const RenderConst& rc;
+    const PathBuffers& pb;
+    BounceCtrl* ctrl;
+    DeferredPush push;
+    __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return qi; }
+    __device__ __forceinline__ void prefetch(int32_t) const {}
+    __device__ __forceinline__ bool load(int32_t pix, d3& o, d3& d, double& t0, double& t1) const {
+        camera_ray(rc, pix, o, d);
+        t0 = 0.0001; /* Camera.cpp:125 */
+        t1 = (double)INFINITY;
+        return true;
+    }
+    __device__ __forceinline__ void flush() {
+        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2], pb.q_mat[3]};
+        push.complete(queues);
+    }
+    __device__ __forceinline__ void retire(bool finished, int32_t pix, const Hit& h) {
+        int cls = -1;
+        if (finished) {
+            int32_t prim;
+            d3 le;
+            const int c = terminal_radiance(S, prim_class, rc, h, prim, le);
+            if (c < CLS_SHADED) {
+                st256g(pb.primary + pix, h.t, h.alpha, h.beta, pack2((uint32_t)prim, (uint32_t)c));
+                cls = c;
+            } else {
+                /* a primary miss returns the background (Camera.cpp:127), an emitter its radiance (:129-132), Empty nothing */
+                st256g(pb.primary + pix, le.x, le.y, le.z, pack2((uint32_t)prim, (uint32_t)c));
+            }
+        }
+        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2], &ctrl->n_mat[3]};
+        push.issue(counters, cls, pix);
+        flush();
+    }
+    __device__ __forceinline__ void finish() {}
+};
+
+template <bool COUNT, int WIDE>
+__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_primary(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb) {
+    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
+    VisitCounters cnt = {0, 0, 0, 0, 0};
+    PrimaryPolicy pol = {S, prim_class, rc, pb, pb.ctrl, {-1, 0, 0, 0}};
+    traverse_persistent<false, COUNT, WIDE>(S, pol, &pb.ctrl->fetch_extend, rc.npix, cnt, sm_stack);
+    flush_counters<COUNT>(cnt, pb.counters);
+}
+
 /* closest hit for every path in the bounce's queue (persistent warps with lane refill,
  * traverse_warp.cuh), then the terminal cases that need no BSDF, then one queue per material class
- * for the shade kernels. Bounce 0 generates its camera rays itself (no ray-generation pass). */
+ * for the shade kernels. Without primary-hit reuse (PRT_RENDER_PIXEL_JITTER) bounce 0 runs here too and
+ * generates its camera rays itself. */
 struct ExtendPolicy {
     static constexpr int REFILL_BELOW = PRT_REFILL_BELOW_RENDER;
     const DevScene& S;
@@ -355,8 +437,9 @@ struct ExtendPolicy {
         if (bounce == 0) {
             camera_ray(rc, slot, o, d);
         } else {
-            o = ld3(pb.rec[slot].o);
-            d = ld3(pb.rec[slot].d);
+            const dd4 s0 = ld256g(rec_sector(pb, slot, 0)), s1 = ld256g(rec_sector(pb, slot, 1));
+            o = mk3(s0.v[0], s0.v[1], s0.v[2]);
+            d = mk3(s0.v[3], s1.v[0], s1.v[1]);
         }
         t0 = 0.0001; /* Camera.cpp:125 */
         t1 = (double)INFINITY;
@@ -370,63 +453,46 @@ struct ExtendPolicy {
         flush();
         int cls = -1;
         if (finished) {
-            PathRec* __restrict__ r = pb.rec + slot;
-            d3 L0 = mk3(0.0, 0.0, 0.0); /* bounce 0 initialises the radiance of every path */
-            if (h.slot < 0) {
-                /* a primary miss returns the background (Camera.cpp:127); with NEE on, a scattered
-                 * ray that misses adds nothing (Camera.cpp:187-196) */
-                const d3 bg = mk3(rc.background[0], rc.background[1], rc.background[2]);
-                if (bounce == 0) L0 = bg;
-                else if (!rc.sample_lights) st3(r->L, ld3(r->L) + ld3(r->T) * bg);
-            } else {
-                const int32_t prim = S.slot_prim[h.slot];
-                const int c = prim_class[prim];
-                if (c == CLS_EMISSIVE) {
-                    /* an emitter ends the path (Camera.cpp:129-132); with NEE on, a scattered ray may
-                     * collect it only if the scattering material skipped light sampling (:191-195) */
-                    const bool take = bounce == 0 || !rc.sample_lights || (r->flags & PRT_FLAG_PREV_SKIP);
-                    if (take) {
-                        const DevMaterial* m = S.materials + S.shade[prim].material;
-                        const d3 le = mk3(m->emission[0], m->emission[1], m->emission[2]);
-                        if (bounce == 0) L0 = le;
-                        else st3(r->L, ld3(r->L) + ld3(r->T) * le);
-                    } else if ((rc.flags & PRT_RENDER_MIS) && r->prev_pdf > 0.f) {
-                        /* PRT_RENDER_MIS: the emitter the reference drops (Camera.cpp:187-196), weighted against the
-                         * light sampler's density for this point (0 if it shows its back). T already holds att / rr. */
-                        const TriShade* __restrict__ sh = S.shade + prim;
-                        const DevMaterial* m = S.materials + sh->material;
-                        const d3 le = mk3(m->emission[0], m->emission[1], m->emission[2]);
-                        const d3 dir = ld3(r->d), n = mk3(sh->normal[0], sh->normal[1], sh->normal[2]);
-                        const double pb = (double)r->prev_pdf;
-                        const double d2 = dot(dir, dir);
-                        const double dn = dot(dir, n);
-                        const double cosl = fabs(dn) / sqrt(d2);
-                        double pl = 0.0;
-                        if (dn < 0.0 && cosl > 0.0) pl = (1.0 / S.lights_area) * (h.t * h.t * d2) / cosl;
-                        st3(r->L, ld3(r->L) + ld3(r->T) * le * (pb / (pb + pl)));
-                    }
-                } else if (c < CLS_SHADED) {
-                    r->hit_prim = prim;
-                    r->hit[0] = h.t;
-                    r->hit[1] = h.alpha;
-                    r->hit[2] = h.beta;
-                    if (bounce == 0) {
-                        r->dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u; /* same sector as the hit */
-#if !PRT_BOUNCE0_LEAN
-                        d3 o, d;
-                        camera_ray(rc, slot, o, d);
-                        st3(r->o, o);
-                        st3(r->d, d);
-                        st3(r->T, mk3(1.0, 1.0, 1.0));
-                        r->flags = 0u;
-                        r->prev_pdf = 0.f;
-#endif
-                    }
-                    cls = c;
+            int32_t prim;
+            d3 le;
+            const int c = terminal_radiance(S, prim_class, rc, h, prim, le);
+            if (c < CLS_SHADED) {
+                st256g(rec_sector(pb, slot, 4), h.t, h.alpha, h.beta, pack2((uint32_t)prim, 0u));
+                if (bounce == 0) lum_set(pb, slot, mk3(0.0, 0.0, 0.0)); /* bounce 0 initialises the radiance of every path */
+                cls = c;
+            } else if (bounce == 0) {
+                lum_set(pb, slot, le); /* background (Camera.cpp:127), emitter (:129-132) or Empty's nothing */
+            } else if (h.slot < 0) {
+                /* with NEE on, a scattered ray that misses adds nothing (Camera.cpp:187-196) */
+                if (!rc.sample_lights) {
+                    const dd4 s1 = ld256g(rec_sector(pb, slot, 1)), s2 = ld256g(rec_sector(pb, slot, 2));
+                    lum_add(pb, slot, mk3(s1.v[2], s1.v[3], s2.v[0]) * le);
                 }
-                /* CLS_EMPTY: no NEE, Scatter returns false (Material.h:537-540): the path ends */
+            } else if (c == CLS_EMISSIVE) {
+                /* an emitter ends the path (Camera.cpp:129-132); with NEE on, a scattered ray may
+                 * collect it only if the scattering material skipped light sampling (:191-195) */
+                const dd4 s1 = ld256g(rec_sector(pb, slot, 1)), s2 = ld256g(rec_sector(pb, slot, 2));
+                const d3 T = mk3(s1.v[2], s1.v[3], s2.v[0]);
+                const bool prev_skip = (unpack_lo(s2.v[1]) >> 31) != 0u;
+                const float prev_pdf = __uint_as_float(unpack_hi(s2.v[1]));
+                if (!rc.sample_lights || prev_skip) {
+                    lum_add(pb, slot, T * le);
+                } else if ((rc.flags & PRT_RENDER_MIS) && prev_pdf > 0.f) {
+                    /* PRT_RENDER_MIS: the emitter the reference drops (Camera.cpp:187-196), weighted against the
+                     * light sampler's density for this point (0 if it shows its back). T already holds att / rr. */
+                    const TriShade* __restrict__ sh = S.shade + prim;
+                    const dd4 s0 = ld256g(rec_sector(pb, slot, 0));
+                    const d3 dir = mk3(s0.v[3], s1.v[0], s1.v[1]), n = mk3(sh->normal[0], sh->normal[1], sh->normal[2]);
+                    const double pbsdf = (double)prev_pdf;
+                    const double d2 = dot(dir, dir);
+                    const double dn = dot(dir, n);
+                    const double cosl = fabs(dn) / sqrt(d2);
+                    double pl = 0.0;
+                    if (dn < 0.0 && cosl > 0.0) pl = (1.0 / S.lights_area) * (h.t * h.t * d2) / cosl;
+                    lum_add(pb, slot, T * le * (pbsdf / (pbsdf + pl)));
+                }
             }
-            if (bounce == 0) st3(r->L, L0);
+            /* CLS_EMPTY past bounce 0: no NEE, Scatter returns false (Material.h:537-540): the path just ends */
         }
         int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2], &ctrl->n_mat[3]};
         push.issue(counters, cls, slot);
@@ -439,60 +505,58 @@ struct ExtendPolicy {
 
 template <bool COUNT, int WIDE>
 __device__ __forceinline__ void extend_body(const DevScene& S, const uint8_t* __restrict__ prim_class, const RenderConst& rc, const PathBuffers& pb,
-                                            int bounce, int sorted, VisitCounters& cnt) {
+                                            int bounce, int sorted, VisitCounters& cnt, int32_t* sm_stack) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = bounce == 0 ? rc.n_paths : __ldcg(&ctrl->n_extend);
     ExtendPolicy pol = {S, prim_class, rc, pb, ctrl, sorted ? pb.qs_extend : pb.q_extend[bounce & 1], bounce, {-1, 0, 0, 0}};
-    traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_extend, n, cnt);
+    traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_extend, n, cnt, sm_stack);
 }
 
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     VisitCounters cnt = {0, 0, 0, 0, 0};
-    extend_body<COUNT, WIDE>(S, prim_class, rc, pb, bounce, sorted, cnt);
+    extend_body<COUNT, WIDE>(S, prim_class, rc, pb, bounce, sorted, cnt, sm_stack);
     flush_counters<COUNT>(cnt, pb.counters);
 }
 
 /* one path vertex of material class CLS (Camera.cpp:134-201). Grid-stride over the class queue with
  * the queue entry read two iterations ahead and the path record prefetched one iteration ahead (the
- * chain queue -> record -> triangle -> material was 30 % of the stall samples, profiles/r1_s1_shade),
- * and both output pushes deferred by one iteration. */
+ * chain queue -> record -> triangle -> material was 30 % of the stall samples, profiles/r1_s1_shade).
+ *
+ * PRIMARY (bounce 0 with primary-hit reuse): the queue holds PIXELS; entry qi names sample qi / nq of pixel
+ * queue[qi % nq], i.e. slot = sample * npix + pixel — sample-major, so that a warp's 32 vertices sit in 32
+ * neighbouring records. The hit comes from the per-pixel table, the ray is recomputed, T = 1, L = 0: the
+ * kernel reads no path record at all. */
 #ifndef PRT_SHADE_MIN_BLOCKS
 #define PRT_SHADE_MIN_BLOCKS 4
 #endif
 #ifndef PRT_SHADE_PREFETCH
 #define PRT_SHADE_PREFETCH 1
 #endif
-#ifndef PRT_SHADE_DEFER
-#define PRT_SHADE_DEFER 0
-#endif
-#ifndef PRT_SHADE_PIPE
-#define PRT_SHADE_PIPE 0 /* measured: shade 8.36 ms against 7.90 ms unpipelined (profiles/r1_s8_ab.txt) */
-#endif
-template <int CLS>
+template <int CLS, bool PRIMARY>
 __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     BounceCtrl* next = pb.ctrl + bounce + 1;
-    const int32_t n = __ldcg(&ctrl->n_mat[CLS]);
+    const int32_t nq = __ldcg(&ctrl->n_mat[CLS]);
+    const int32_t n = PRIMARY ? nq * rc.n_samples : nq;
     const int32_t* queue = pb.q_mat[CLS]; /* ld.cg, as in ExtendPolicy */
     int32_t* const out_q[2] = {pb.q_shadow, pb.q_extend[(bounce + 1) & 1]};
     int32_t* const out_n[2] = {&ctrl->n_shadow, &next->n_extend};
     const int32_t n_round = (n + 31) & ~31;
     const int32_t stride = gridDim.x * blockDim.x;
+    /* the slot that queue position q names, -1 past the end */
+    auto entry = [&](int64_t q) -> int32_t {
+        if (q >= (int64_t)n) return -1;
+        if (PRIMARY) {
+            const int32_t s = (int32_t)q / nq;
+            return s * rc.npix + __ldcg(queue + ((int32_t)q - s * nq));
+        }
+        return __ldcg(queue + q);
+    };
     int32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
-    int32_t slot_next = qi < n ? __ldcg(queue + qi) : -1;
-    int32_t slot_next2 = qi + stride < n ? __ldcg(queue + qi + stride) : -1;
-#if PRT_SHADE_PIPE
-    /* software pipeline over the dependent chain queue -> record -> triangle -> material (half of the
-     * long-scoreboard samples of the unpipelined loop, profiles/r1_s7_shade): queue entries are read
-     * three iterations ahead, the record is prefetched two ahead, its primitive id read one ahead
-     * and that triangle's material index fetched at the end of the iteration before, so an
-     * iteration starts with every address it needs already in registers */
-    int32_t slot_next3 = (int64_t)qi + 2 * (int64_t)stride < n ? __ldcg(queue + qi + 2 * stride) : -1;
-    if (slot_next2 >= 0) prefetch_l2(pb.rec + slot_next2);
-    int32_t prim_next = slot_next >= 0 ? __ldcg(&pb.rec[slot_next].hit_prim) : -1;
-    int32_t mat_next = prim_next >= 0 ? __ldg(&S.shade[prim_next].material) : 0;
-#endif
+    int32_t slot_next = entry(qi);
+    int32_t slot_next2 = entry((int64_t)qi + stride);
     DeferredPush push_shadow, push_extend;
     push_shadow.init();
     push_extend.init();
@@ -501,47 +565,47 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
         uint32_t key_shadow = 0, key_extend = 0;
         const int32_t slot = slot_next;
         slot_next = slot_next2;
-#if PRT_SHADE_PIPE
-        const int32_t prim_cur = prim_next, mat_cur = mat_next;
-        slot_next2 = slot_next3;
-        slot_next3 = (int64_t)qi + 3 * (int64_t)stride < n ? __ldcg(queue + qi + 3 * stride) : -1;
-        if (slot_next2 >= 0) prefetch_l2(pb.rec + slot_next2);
-        prim_next = slot_next >= 0 ? __ldcg(&pb.rec[slot_next].hit_prim) : -1;
-#else
-        slot_next2 = (int64_t)qi + 2 * (int64_t)stride < n ? __ldcg(queue + qi + 2 * stride) : -1;
-#endif
-#if PRT_SHADE_PREFETCH && !PRT_SHADE_PIPE
-#ifndef PRT_LEAN_PREFETCH0
-#define PRT_LEAN_PREFETCH0 1 /* 0: no prefetch at bounce 0 (the queue is in slot order there) */
-#endif
-        if (slot_next >= 0 && (PRT_LEAN_PREFETCH0 || !PRT_BOUNCE0_LEAN || bounce != 0)) {
-            prefetch_l2(PRT_BOUNCE0_LEAN && bounce == 0 ? (const void*)pb.rec[slot_next].hit : (const void*)(pb.rec + slot_next));
-#if PRT_SHADE_PREFETCH > 1
-            prefetch_l2(reinterpret_cast<const char*>(pb.rec + slot_next) + 128);
-#endif
+        slot_next2 = entry((int64_t)qi + 2 * (int64_t)stride);
+#if PRT_SHADE_PREFETCH
+        if (!PRIMARY && slot_next >= 0) {
+            if (bounce == 0) {
+                prefetch_l2(rec_sector(pb, slot_next, 4)); /* bounce 0 without reuse reads the hit only */
+            } else {
+                prefetch_l2(rec_sector(pb, slot_next, 0)); /* 160 B: two 128-byte lines at most */
+                prefetch_l2(rec_sector(pb, slot_next, 4));
+            }
         }
 #endif
         if (slot >= 0) {
-            PathRec* __restrict__ r = pb.rec + slot;
-#if PRT_SHADE_PIPE
-            const int32_t prim = prim_cur;
-            const TriShade* __restrict__ sh = S.shade + prim;
-            const DevMaterial m = S.materials[mat_cur];
-#else
-            const int32_t prim = r->hit_prim;
+            /* ---- the vertex: hit, incoming ray, throughput, RNG dimension ---- */
+            int32_t prim;
+            double t, alpha, beta;
+            d3 ro, rd, T;
+            uint32_t dim;
+            if (PRIMARY) {
+                const dd4 ph = ld256d(pb.primary + (slot % rc.npix)); /* written by the previous launch: read-only here */
+                t = ph.v[0]; alpha = ph.v[1]; beta = ph.v[2];
+                prim = (int32_t)unpack_lo(ph.v[3]);
+            } else {
+                const dd4 s4 = ld256g(rec_sector(pb, slot, 4));
+                t = s4.v[0]; alpha = s4.v[1]; beta = s4.v[2];
+                prim = (int32_t)unpack_lo(s4.v[3]);
+            }
+            if (PRIMARY || bounce == 0) {
+                /* bounce 0: the camera ray and T = 1 are recomputed instead of being written by the extend stage and
+                 * read back; the stream starts at dimension 0 (2 after the jitter draws) */
+                camera_ray(rc, slot, ro, rd);
+                T = mk3(1.0, 1.0, 1.0);
+                dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u;
+            } else {
+                const dd4 s0 = ld256g(rec_sector(pb, slot, 0)), s1 = ld256g(rec_sector(pb, slot, 1)), s2 = ld256g(rec_sector(pb, slot, 2));
+                ro = mk3(s0.v[0], s0.v[1], s0.v[2]);
+                rd = mk3(s0.v[3], s1.v[0], s1.v[1]);
+                T = mk3(s1.v[2], s1.v[3], s2.v[0]);
+                dim = unpack_lo(s2.v[1]) & 0x7fffffffu;
+            }
             const TriShade* __restrict__ sh = S.shade + prim;
             const DevMaterial m = S.materials[sh->material];
-#endif
-            const double t = r->hit[0], alpha = r->hit[1], beta = r->hit[2];
-#if PRT_BOUNCE0_LEAN
-            /* bounce 0: the camera ray and T = 1 are recomputed here instead of being written by k_extend and
-             * read back (96 B less read here, 64 B less written there, per path: the two launches are DRAM-bound) */
-            d3 ro, rd;
-            if (bounce == 0) camera_ray(rc, slot, ro, rd);
-            else { ro = ld3(r->o); rd = ld3(r->d); }
-#else
-            const d3 ro = ld3(r->o), rd = ld3(r->d);
-#endif
             /* the HitRecord of Triangle::Hit (Triangle.cpp:76-80,111) */
             Surface s;
             s.position = ro + rd * t;
@@ -554,14 +618,10 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
 
             Rng rng;
             rng.seed = stream_seed(rc.rng_key, (uint32_t)(slot % rc.npix), (uint32_t)(rc.sample_first + slot / rc.npix));
-            rng.dim = r->dim;
-#if PRT_BOUNCE0_LEAN
-            const d3 T = bounce == 0 ? mk3(1.0, 1.0, 1.0) : ld3(r->T);
-#else
-            const d3 T = ld3(r->T);
-#endif
+            rng.dim = dim;
 
             /* ---- next-event estimation (Camera.cpp:137-174) ---- */
+            d3 lp = mk3(0.0, 0.0, 0.0), sc = mk3(0.0, 0.0, 0.0);
             if (rc.sample_lights && !m.skip_light_sampling) {
                 const double u0 = rng.next(), u1 = rng.next(), u2 = rng.next(), u3 = rng.next();
                 LightSample ls;
@@ -581,54 +641,52 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
                     if ((rc.flags & PRT_RENDER_MIS) && (CLS == CLS_LAMBERT || (CLS == CLS_PHONG && m.pkd == 1.0))) {
                         /* balance heuristic against the cosine lobe's density for the same direction */
                         const double pl = ls.pdf * (distance * distance) / cos_theta_bar;
-                        const double pb = cos_theta * PRT_INV_PI;
-                        direct = direct * (pl / (pl + pb));
+                        const double pbsdf = cos_theta * PRT_INV_PI;
+                        direct = direct * (pl / (pl + pbsdf));
                     }
-                    st3(r->sdir, light_dir);
-                    r->sdist = distance;
-                    st3(r->scontrib, T * direct);
+                    /* the shadow ray is stored as its target: k_shadow recomputes light_dir and distance from
+                     * (lp, o = s.position) with the functions used above */
+                    lp = ls.position;
+                    sc = T * direct;
                     want_shadow = true;
                     if (sort) key_shadow = ray_key(rc.key_lo, rc.key_scale, s.position, light_dir);
                 }
             }
             /* ---- Russian roulette + BSDF sampling (Camera.cpp:176-201) ---- */
+            d3 out_dir = rd, Tn = T;
+            uint32_t dimflags = dim;
+            float prev_pdf = 0.f;
             if (rng.next() < rc.rr) {
-                d3 att, out_dir;
+                d3 att, sd;
                 bool scattered = true;
                 double cosine_pdf = 0.0;
-                if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, out_dir, cosine_pdf);
-                else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, out_dir, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
-                else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, out_dir);
-                else scatter_mirror(s, wo, att, out_dir);
+                if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, sd, cosine_pdf);
+                else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, sd, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
+                else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, sd);
+                else scatter_mirror(s, wo, att, sd);
                 /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
                 if (scattered && bounce < rc.max_depth) {
-                    st3(r->o, s.position);
-                    st3(r->d, out_dir);
-                    st3(r->T, T * att / rc.rr);
-                    r->dim = rng.dim;
-                    r->flags = m.skip_light_sampling ? PRT_FLAG_PREV_SKIP : 0u;
-                    r->prev_pdf = (rc.flags & PRT_RENDER_MIS) ? (float)cosine_pdf : 0.f;
+                    out_dir = sd;
+                    Tn = T * att / rc.rr;
+                    dimflags = rng.dim | (m.skip_light_sampling ? 0x80000000u : 0u);
+                    prev_pdf = (rc.flags & PRT_RENDER_MIS) ? (float)cosine_pdf : 0.f;
                     want_extend = true;
                     if (sort) key_extend = ray_key(rc.key_lo, rc.key_scale, s.position, out_dir);
                 }
             }
-            if (want_shadow && !want_extend) st3(r->o, s.position); /* shadow ray origin */
+            /* ---- the record: whole sectors, only those a later stage reads ---- */
+            if (want_extend || want_shadow) st256g(rec_sector(pb, slot, 0), s.position.x, s.position.y, s.position.z, out_dir.x);
+            if (want_extend) st256g(rec_sector(pb, slot, 1), out_dir.y, out_dir.z, Tn.x, Tn.y);
+            if (want_extend || want_shadow) st256g(rec_sector(pb, slot, 2), Tn.z, pack2(dimflags, __float_as_uint(prev_pdf)), lp.x, lp.y);
+            if (want_shadow) st256g(rec_sector(pb, slot, 3), lp.z, sc.x, sc.y, sc.z);
+            if (PRIMARY) lum_set(pb, slot, mk3(0.0, 0.0, 0.0)); /* bounce 0 initialises the radiance of every path */
         }
-#if PRT_SHADE_PIPE
-        mat_next = prim_next >= 0 ? __ldg(&S.shade[prim_next].material) : 0;
-#endif
         __syncwarp();
         {
             int32_t* const q0[1] = {out_q[0]};
             int32_t* const q1[1] = {out_q[1]};
             int32_t* const n0[1] = {out_n[0]};
             int32_t* const n1[1] = {out_n[1]};
-#if PRT_SHADE_DEFER
-            push_shadow.complete(q0);
-            push_extend.complete(q1);
-            push_shadow.issue(n0, want_shadow ? 0 : -1, slot);
-            push_extend.issue(n1, want_extend ? 0 : -1, slot);
-#else
             push_shadow.issue(n0, want_shadow ? 0 : -1, slot);
             push_extend.issue(n1, want_extend ? 0 : -1, slot);
             if (sort) {
@@ -643,20 +701,13 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
                 push_shadow.complete(q0);
                 push_extend.complete(q1);
             }
-#endif
         }
-    }
-    {
-        int32_t* const q0[1] = {out_q[0]};
-        int32_t* const q1[1] = {out_q[1]};
-        push_shadow.complete(q0);
-        push_extend.complete(q1);
     }
 }
 
-template <int CLS>
+template <int CLS, bool PRIMARY>
 __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sort) {
-    shade_body<CLS>(S, rc, pb, bounce, sort);
+    shade_body<CLS, PRIMARY>(S, rc, pb, bounce, sort);
 }
 
 /* NEE visibility (Camera.cpp:143-155). The reference asks for the closest hit on [1e-3, DBL_MAX]
@@ -672,19 +723,22 @@ struct ShadowPolicy {
     double distance;
     __device__ __forceinline__ int32_t slot_of(int32_t qi) const { return __ldcg(queue + qi); }
     __device__ __forceinline__ void prefetch(int32_t slot) const {
-        prefetch_l2(pb.rec + slot);
-        prefetch_l2(reinterpret_cast<const char*>(pb.rec + slot) + 128);
+        prefetch_l2(rec_sector(pb, slot, 0));
+        prefetch_l2(rec_sector(pb, slot, 3));
     }
     __device__ __forceinline__ void finish() const {}
     __device__ __forceinline__ bool load(int32_t slot, d3& o, d3& d, double& t0, double& t1) {
-        /* by now the record holds the hit position as the origin of the next segment */
-        ps = ld3(pb.rec[slot].o);
-        dir = ld3(pb.rec[slot].sdir);
-        distance = pb.rec[slot].sdist;
-        o = ps;
-        d = dir;
+        /* by now the record holds the hit position as the origin of the next segment, and the light sample */
+        const dd4 s0 = ld256g(rec_sector(pb, slot, 0)), s2 = ld256g(rec_sector(pb, slot, 2)), s3 = ld256g(rec_sector(pb, slot, 3));
+        const d3 p = mk3(s0.v[0], s0.v[1], s0.v[2]);
+        const d3 to_light = mk3(s2.v[2], s2.v[3], s3.v[0]) - p; /* Camera.cpp:141-143, as in k_shade */
+        const d3 light_dir = normalize(to_light);
+        const double dist = length(to_light);
+        if (EXACT) { ps = p; dir = light_dir; distance = dist; }
+        o = p;
+        d = light_dir;
         t0 = 0.001;
-        t1 = EXACT ? DBL_MAX : distance - 0.001;
+        t1 = EXACT ? DBL_MAX : dist - 0.001;
         return true;
     }
     __device__ __forceinline__ void retire(bool finished, int32_t slot, const Hit& h) {
@@ -699,27 +753,32 @@ struct ShadowPolicy {
         } else {
             visible = h.slot < 0;
         }
-        if (visible) st3(pb.rec[slot].L, ld3(pb.rec[slot].L) + ld3(pb.rec[slot].scontrib));
+        if (visible) {
+            const dd4 s3 = ld256g(rec_sector(pb, slot, 3));
+            lum_add(pb, slot, mk3(s3.v[1], s3.v[2], s3.v[3]));
+        }
     }
 };
 
 template <bool COUNT, int WIDE>
-__device__ __forceinline__ void shadow_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sorted, VisitCounters& cnt) {
+__device__ __forceinline__ void shadow_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sorted, VisitCounters& cnt,
+                                            int32_t* sm_stack) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     const int32_t n = __ldcg(&ctrl->n_shadow);
     if (rc.flags & PRT_RENDER_EXACT_VISIBILITY) {
         ShadowPolicy<true> pol = {pb, sorted ? pb.qs_shadow : pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
-        traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
+        traverse_persistent<false, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt, sm_stack);
     } else {
         ShadowPolicy<false> pol = {pb, sorted ? pb.qs_shadow : pb.q_shadow, mk3(0, 0, 0), mk3(0, 0, 0), 0.0};
-        traverse_persistent<true, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt);
+        traverse_persistent<true, COUNT, WIDE>(S, pol, &ctrl->fetch_shadow, n, cnt, sm_stack);
     }
 }
 
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     VisitCounters cnt = {0, 0, 0, 0, 0};
-    shadow_body<COUNT, WIDE>(S, rc, pb, bounce, sorted, cnt);
+    shadow_body<COUNT, WIDE>(S, rc, pb, bounce, sorted, cnt, sm_stack);
     flush_counters<COUNT>(cnt, pb.counters);
 }
 
@@ -730,43 +789,61 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScen
  * (profiles/r1_s5_launches.csv). From bounce `first` on, the same stage bodies run back to back
  * inside this kernel, separated by grid-wide barriers, until the extend queue is empty. Results are
  * those of the per-bounce launches (same code, same queues); only launch count and idle time change.
- * The barrier after the shadow stage is needed: shadow(b) and extend(b + 1) both update rec.L. */
+ * The barrier after the shadow stage is needed: shadow(b) and extend(b + 1) both update the radiance cells. */
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, 2) k_tail(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int first) {
+    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     cg::grid_group grid = cg::this_grid();
     VisitCounters cnt = {0, 0, 0, 0, 0};
     for (int b = first; b <= rc.max_depth; ++b) {
         if (b > 0 && __ldcg(&pb.ctrl[b].n_extend) == 0) break; /* uniform: written before the last barrier */
-        extend_body<COUNT, WIDE>(S, prim_class, rc, pb, b, 0, cnt);
+        extend_body<COUNT, WIDE>(S, prim_class, rc, pb, b, 0, cnt, sm_stack);
         grid.sync();
-        if (rc.class_mask & (1 << CLS_LAMBERT)) shade_body<CLS_LAMBERT>(S, rc, pb, b, 0);
-        if (rc.class_mask & (1 << CLS_PHONG)) shade_body<CLS_PHONG>(S, rc, pb, b, 0);
-        if (rc.class_mask & (1 << CLS_MIRROR)) shade_body<CLS_MIRROR>(S, rc, pb, b, 0);
-        if (rc.class_mask & (1 << CLS_COOK)) shade_body<CLS_COOK>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_LAMBERT)) shade_body<CLS_LAMBERT, false>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_PHONG)) shade_body<CLS_PHONG, false>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_MIRROR)) shade_body<CLS_MIRROR, false>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_COOK)) shade_body<CLS_COOK, false>(S, rc, pb, b, 0);
         grid.sync();
         if (rc.sample_lights) {
-            shadow_body<COUNT, WIDE>(S, rc, pb, b, 0, cnt);
+            shadow_body<COUNT, WIDE>(S, rc, pb, b, 0, cnt, sm_stack);
             grid.sync();
         }
     }
     flush_counters<COUNT>(cnt, pb.counters);
 }
 
-/* colorAttachment[m] += RayColor * pixelSamplesScale, samples in index order (Camera.cpp:54-57) */
+/* colorAttachment[m] += RayColor * pixelSamplesScale, samples in index order (Camera.cpp:54-57). Streams the
+ * radiance plane (consecutive threads = consecutive pixels = consecutive 32-byte cells); a pixel whose path ended
+ * at bounce 0 under primary-hit reuse has no cells: all its samples returned the table's radiance. */
 __global__ void __launch_bounds__(256) k_accumulate(RenderConst rc, PathBuffers pb, double* __restrict__ rgb) {
     for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < rc.npix; pix += gridDim.x * blockDim.x) {
         d3 acc = mk3(rgb[3 * (int64_t)pix], rgb[3 * (int64_t)pix + 1], rgb[3 * (int64_t)pix + 2]);
-        for (int s = 0; s < rc.n_samples; ++s) acc = acc + ld3(pb.rec[(int64_t)s * rc.npix + pix].L) * rc.scale;
+        bool constant = false;
+        d3 c = mk3(0.0, 0.0, 0.0);
+        if (rc.primary_reuse) {
+            const dd4 ph = ld256d(pb.primary + pix);
+            constant = (int32_t)unpack_hi(ph.v[3]) >= CLS_SHADED;
+            c = mk3(ph.v[0], ph.v[1], ph.v[2]);
+        }
+        if (constant) {
+            const d3 term = c * rc.scale;
+            for (int s = 0; s < rc.n_samples; ++s) acc = acc + term;
+        } else {
+            for (int s = 0; s < rc.n_samples; ++s) {
+                const dd4 l = ld256g(pb.lum + ((int64_t)s * rc.npix + pix));
+                acc = acc + mk3(l.v[0], l.v[1], l.v[2]) * rc.scale;
+            }
+        }
         rgb[3 * (int64_t)pix] = acc.x; rgb[3 * (int64_t)pix + 1] = acc.y; rgb[3 * (int64_t)pix + 2] = acc.z;
     }
 }
 
 /* ray accounting of one pass, kept on the device so that the render call stays asynchronous:
  * totals[2] += extend rays, totals[3] += shadow rays */
-__global__ void k_pass_stats(const BounceCtrl* __restrict__ ctrl, int n_bounces, int n_paths, unsigned long long* totals) {
+__global__ void k_pass_stats(const BounceCtrl* __restrict__ ctrl, int n_bounces, int n_rays0, unsigned long long* totals) {
     unsigned long long e = 0, s = 0;
     for (int b = threadIdx.x; b < n_bounces; b += 32) {
-        e += b == 0 ? (unsigned long long)n_paths : (unsigned long long)ctrl[b].n_extend;
+        e += b == 0 ? (unsigned long long)n_rays0 : (unsigned long long)ctrl[b].n_extend; /* bounce 0: one ray per path, or per pixel under primary-hit reuse */
         s += (unsigned long long)ctrl[b].n_shadow;
     }
     for (int o = 16; o > 0; o >>= 1) {
@@ -807,19 +884,25 @@ __global__ void __launch_bounds__(256) k_resolve(const double* __restrict__ rgb,
 
 /* persistent kernels get exactly as many blocks as can be resident (148 SMs x occupancy), never a
  * second wave; small queues get fewer */
+/* resident blocks per SM of `kernel` on the CURRENT device, looked up once per (device, kernel). Contexts on
+ * different GPUs render from different host threads (prt_render_multi): the cache is keyed by device and locked. */
+static int blocks_per_sm(const void* kernel, int block) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, int> cache;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lock(mu);
+    const auto key = std::make_pair(dev, kernel);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    cache[key] = per_sm;
+    return per_sm;
+}
 template <typename K>
 static int persistent_grid(K kernel, int block, const LaunchConfig& lc, int64_t items) {
-    static std::unordered_map<const void*, int> cache;
-    const void* key = (const void*)kernel;
-    auto it = cache.find(key);
-    int per_sm;
-    if (it == cache.end()) {
-        per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
-        cache[key] = per_sm;
-    } else {
-        per_sm = it->second;
-    }
+    int per_sm = blocks_per_sm((const void*)kernel, block);
     if (lc.trace_blocks_per_sm > 0 && per_sm > lc.trace_blocks_per_sm) per_sm = lc.trace_blocks_per_sm;
     const int64_t cap = (int64_t)per_sm * lc.sm_count;
     int64_t want = (items + block - 1) / block;
@@ -887,32 +970,42 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int wide = wide_of(S);
     LaunchConfig shade_lc = lc;
     shade_lc.trace_blocks_per_sm = 0;
-    const int g_shade0 = persistent_grid(k_shade<CLS_LAMBERT>, 128, shade_lc, rc.n_paths);
-    const int g_shade1 = persistent_grid(k_shade<CLS_PHONG>, 128, shade_lc, rc.n_paths);
-    const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR>, 128, shade_lc, rc.n_paths);
-    const int g_shade3 = persistent_grid(k_shade<CLS_COOK>, 128, shade_lc, rc.n_paths);
+    const int g_shade0 = persistent_grid(k_shade<CLS_LAMBERT, false>, 128, shade_lc, rc.n_paths);
+    const int g_shade1 = persistent_grid(k_shade<CLS_PHONG, false>, 128, shade_lc, rc.n_paths);
+    const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR, false>, 128, shade_lc, rc.n_paths);
+    const int g_shade3 = persistent_grid(k_shade<CLS_COOK, false>, 128, shade_lc, rc.n_paths);
     cudaEvent_t* ev = lc.stage_events;
     /* Both per-bounce decisions are taken here from the EXPECTED queue length n_paths * rr^bounce
      * (Russian roulette thins the wavefront geometrically; the host never reads a queue length back):
      *   - ray binning for long queues (off by default, launch.h);
      *   - the first bounce of the tail: once fewer than lc.tail_paths paths are expected, the rest of
-     *     the pass runs inside ONE cooperative launch (k_tail). */
+     *     the pass runs inside ONE cooperative launch (k_tail). Under primary-hit reuse bounce 0 always has its
+     *     own launches (its extend stage is per pixel, its shade stage expands pixels into samples). */
     const double survive = rc.rr < 1.0 ? (rc.rr > 0.0 ? rc.rr : 0.0) : 1.0;
     double expect = (double)rc.n_paths;
     int sorted = 0; /* this bounce's extend queue was reordered by the previous bounce */
     const int sort_grid = (int)std::min<int64_t>((rc.n_paths + 255) / 256, (int64_t)lc.sm_count * 8);
     int b = 0;
     for (; b < n_bounces; ++b) {
-        if (lc.tail_paths > 0 && expect < (double)lc.tail_paths) break;
+        const bool primary = b == 0 && rc.primary_reuse;
+        if (!primary && lc.tail_paths > 0 && expect < (double)lc.tail_paths) break;
         const int sort = lc.sort_min > 0 && expect >= (double)lc.sort_min ? 1 : 0;
         if (ev) cudaEventRecord(ev[4 * b], st);
-        PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, prim_class, rc, pb, b, sorted));
+        if (primary) PRT_DISPATCH(count, wide, k_primary, persistent_grid(KERNEL, 128, lc, rc.npix), (S, prim_class, rc, pb));
+        else PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, prim_class, rc, pb, b, sorted));
         ++launches;
         if (ev) cudaEventRecord(ev[4 * b + 1], st);
-        if (rc.class_mask & (1 << CLS_LAMBERT)) { k_shade<CLS_LAMBERT><<<g_shade0, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
-        if (rc.class_mask & (1 << CLS_PHONG)) { k_shade<CLS_PHONG><<<g_shade1, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
-        if (rc.class_mask & (1 << CLS_MIRROR)) { k_shade<CLS_MIRROR><<<g_shade2, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
-        if (rc.class_mask & (1 << CLS_COOK)) { k_shade<CLS_COOK><<<g_shade3, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+        if (primary) {
+            if (rc.class_mask & (1 << CLS_LAMBERT)) { k_shade<CLS_LAMBERT, true><<<persistent_grid(k_shade<CLS_LAMBERT, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_PHONG)) { k_shade<CLS_PHONG, true><<<persistent_grid(k_shade<CLS_PHONG, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_MIRROR)) { k_shade<CLS_MIRROR, true><<<persistent_grid(k_shade<CLS_MIRROR, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_COOK)) { k_shade<CLS_COOK, true><<<persistent_grid(k_shade<CLS_COOK, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+        } else {
+            if (rc.class_mask & (1 << CLS_LAMBERT)) { k_shade<CLS_LAMBERT, false><<<g_shade0, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_PHONG)) { k_shade<CLS_PHONG, false><<<g_shade1, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_MIRROR)) { k_shade<CLS_MIRROR, false><<<g_shade2, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_COOK)) { k_shade<CLS_COOK, false><<<g_shade3, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+        }
         if (sort) {
             BounceCtrl* dc = pb.ctrl + b;
             const SortJob je = {&(dc + 1)->n_extend, 0, pb.key_extend, pb.q_extend[(b + 1) & 1], pb.qs_extend};
@@ -943,16 +1036,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         void* args[] = {(void*)&S_, (void*)&pc_, (void*)&rc_, (void*)&pb_, (void*)&first};
         const void* fn = count ? (wide == 40 ? (const void*)k_tail<true, 40> : (wide == 4 ? (const void*)k_tail<true, 4> : (const void*)k_tail<true, 2>))
                                : (wide == 40 ? (const void*)k_tail<false, 40> : (wide == 4 ? (const void*)k_tail<false, 4> : (const void*)k_tail<false, 2>));
-        static std::unordered_map<const void*, int> occ;
-        int per_sm;
-        auto it = occ.find(fn);
-        if (it == occ.end()) {
-            per_sm = 0;
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 128, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
-            occ[fn] = per_sm;
-        } else {
-            per_sm = it->second;
-        }
+        int per_sm = blocks_per_sm(fn, 128);
         if (per_sm > 2) per_sm = 2;
         int64_t want = (rc.n_paths + 127) / 128;
         const int64_t cap = (int64_t)per_sm * lc.sm_count;
@@ -963,7 +1047,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         if (ev) cudaEventRecord(ev[4 * b + 1], st);
     }
     k_accumulate<<<(rc.npix + 255) / 256 < lc.sm_count * 8 ? (rc.npix + 255) / 256 : lc.sm_count * 8, 256, 0, st>>>(rc, pb, rgb);
-    k_pass_stats<<<1, 32, 0, st>>>(pb.ctrl, n_bounces, rc.n_paths, totals);
+    k_pass_stats<<<1, 32, 0, st>>>(pb.ctrl, n_bounces, rc.primary_reuse ? rc.npix : rc.n_paths, totals);
     launches += 2;
     return launches;
 }

@@ -21,7 +21,9 @@
 
 namespace prt {
 
-#define PRT_STACK 64
+#ifndef PRT_STACK
+#define PRT_STACK 64 /* the reference-order walk's stack: depth = log2(mesh size) + the top level, 64 covers any mesh that fits */
+#endif
 #define PRT_NO_CHILD INT32_MIN
 
 struct Hit {
@@ -61,6 +63,23 @@ __device__ __forceinline__ dd4 ld256d(const void* p) {
     asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.v[0]), "=d"(r.v[1]), "=d"(r.v[2]), "=d"(r.v[3]) : "l"(p));
     return r;
 }
+
+/* 256-bit loads / stores of MUTABLE global data (the wavefront's path records, launch.h): coherent (no .nc:
+ * k_tail rewrites records between the stages of one launch), and kept out of L1 on the way in — a record is
+ * read once per kernel, the L1 belongs to the BVH nodes and triangles every ray shares. One request per
+ * 32-byte sector of a lane's record instead of four 64-bit ones. */
+__device__ __forceinline__ dd4 ld256g(const void* p) {
+    dd4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.v[0]), "=d"(r.v[1]), "=d"(r.v[2]), "=d"(r.v[3]) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void st256g(void* p, double a, double b, double c, double d) {
+    asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+/* two 32-bit words <-> one FP64 register image (a record's packed integer fields ride in vector loads) */
+__device__ __forceinline__ double pack2(uint32_t lo, uint32_t hi) { return __hiloint2double((int)hi, (int)lo); }
+__device__ __forceinline__ uint32_t unpack_lo(double v) { return (uint32_t)__double2loint(v); }
+__device__ __forceinline__ uint32_t unpack_hi(double v) { return (uint32_t)__double2hiint(v); }
 
 /* Triangle::Hit. The 128-byte record is read as the plane (32 B) first and the remaining 96 B
  * only for candidates whose t is inside the interval. */
@@ -145,7 +164,10 @@ __device__ __forceinline__ void trace_reference(const DevScene& S, d3 o, d3 d, d
             if (ok) {
                 /* left, then right (BVH.cpp:57-58); a span-1 node has left == right (BVH.cpp:21-24)
                  * and testing the same object again with max = its own t changes nothing */
-                if (ch.y != ch.x && sp < PRT_STACK) stack[sp++] = ch.y;
+                if (ch.y != ch.x) {
+                    if (sp < PRT_STACK) stack[sp++] = ch.y;
+                    else if (S.ref_overflow) atomicAdd(S.ref_overflow, 1ull); /* a dropped subtree is an ERROR: sticky, prt_get_stats reports it */
+                }
                 cur = ch.x;
                 continue;
             }

@@ -47,6 +47,19 @@ namespace prt {
 #define PRT_SAH_STACK 64         /* entries of the SAH / LBVH walk's stack; a ray that overflows it is handed to the
                                     reference-order walk (whose own depth is bounded by log2 of the mesh sizes) */
 #endif
+/* The first PRT_SMEM_STACK entries of a lane's stack live in SHARED memory, laid out [entry][thread] so that a
+ * lane's bank never changes and no two lanes of a warp share one: conflict-free at any mix of stack depths. The
+ * round-1 stack was a 64-entry local-memory array: 107-128 M local loads + 58-70 M local stores per k_extend
+ * launch (profiles/r1_s26_extend_ncu_summary.txt) through the same L1TEX pipe the node and triangle fetches
+ * saturate (75-88 %). Deeper entries (a BVH4 walk pushes up to three per level; cornell-box stays below 12,
+ * the 10 M-triangle meshes below 30) spill to a local array, so depth is never lost; beyond PRT_SAH_STACK the
+ * ray goes to the reference-order walk as before. */
+#ifndef PRT_SMEM_STACK
+#define PRT_SMEM_STACK 16
+#endif
+#define PRT_TRAVERSE_BLOCK 128 /* threads per block of every kernel that walks the tree */
+#define PRT_SMEM_STACK_WORDS (((PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) > 0 ? (PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) : 1) * PRT_TRAVERSE_BLOCK)
+
 /* refill idle lanes once fewer than this many lanes hold a ray (Policy::REFILL_BELOW). Refilling early keeps
  * lanes busy; refilling late keeps the rays of a warp (and the path vertices they push for k_shade) together.
  * Measured (profiles/r1_s8_ab.txt): the render kernels like 8-12 (k_shade reads the records of consecutive
@@ -246,12 +259,23 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
  * trace_reference before they are retired.
  */
 template <bool ANY, bool COUNT, int WIDE, class P>
-__device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, int32_t* cursor, int32_t n, VisitCounters& cnt) {
+__device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, int32_t* cursor, int32_t n, VisitCounters& cnt, int32_t* sm_stack) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
-    int32_t stack[PRT_SAH_STACK];
+    constexpr int SM_N = PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK;
+    constexpr int LOC_N = PRT_SAH_STACK - SM_N > 0 ? PRT_SAH_STACK - SM_N : 1;
+    int32_t* const sm = sm_stack + threadIdx.x; /* entry e of this lane: sm[e * PRT_TRAVERSE_BLOCK] */
+    int32_t deep[LOC_N];                        /* entries SM_N .. PRT_SAH_STACK - 1 (rarely reached) */
     int sp = 0;
+#define PRT_PUSH(v)                                                     \
+    do {                                                                \
+        if (sp < SM_N) sm[sp * PRT_TRAVERSE_BLOCK] = (v);               \
+        else if (sp < PRT_SAH_STACK) deep[sp - SM_N] = (v);             \
+        else { overflow = true; break; }                                \
+        ++sp;                                                           \
+    } while (0)
+#define PRT_POP() (--sp, sp < SM_N ? sm[sp * PRT_TRAVERSE_BLOCK] : deep[sp - SM_N])
     int32_t cur = PRT_DONE;
     int32_t leaf = -1; /* PRT_WALK_MODE 1: parked leaf, (slot << 3) | (triangles left - 1) */
     int32_t slot = -1;
@@ -394,19 +418,19 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                 const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
                 if (h0 && h1) {
                     const bool swap = e1 < e0;
-                    if (sp < PRT_SAH_STACK) stack[sp++] = swap ? ch.x : ch.y; else overflow = true;
+                    PRT_PUSH(swap ? ch.x : ch.y);
                     cur = swap ? ch.y : ch.x;
                 } else if (h0) {
                     cur = ch.x;
                 } else if (h1) {
                     cur = ch.y;
                 } else {
-                    cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                    cur = sp > 0 ? PRT_POP() : PRT_DONE;
                 }
             }
             if (cur < 0 && leaf < 0) { /* park the leaf, go on with the stack */
                 leaf = ~cur;
-                cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                cur = sp > 0 ? PRT_POP() : PRT_DONE;
             }
             const unsigned lm = __ballot_sync(FULL, leaf >= 0);
             const unsigned im = __ballot_sync(FULL, cur >= 0 && cur != PRT_DONE);
@@ -497,15 +521,12 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                         const unsigned s1 = min(t1, t2), s2 = max(t1, t2);
 #define PRT_CHILD_OF(key) (((key) & 2u) ? (((key) & 1u) ? ch.w : ch.z) : (((key) & 1u) ? ch.y : ch.x))
                         if (s0 == MISS) {
-                            cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                            cur = sp > 0 ? PRT_POP() : PRT_DONE;
                         } else {
-                            if (s3 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s3); else overflow = true; }
-                            if (s2 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s2); else overflow = true; }
-                            if (s1 != MISS) { if (sp < PRT_SAH_STACK) stack[sp++] = PRT_CHILD_OF(s1); else overflow = true; }
+                            if (s3 != MISS) PRT_PUSH(PRT_CHILD_OF(s3));
+                            if (s2 != MISS) PRT_PUSH(PRT_CHILD_OF(s2));
+                            if (s1 != MISS) PRT_PUSH(PRT_CHILD_OF(s1));
                             cur = PRT_CHILD_OF(s0);
-#if PRT_PREFETCH_PUSH
-                            if (s1 != MISS && stack[sp - 1] >= 0) prefetch_line(WIDE == 40 ? (const void*)(S.nodes4q + stack[sp - 1]) : (const void*)(S.nodes4 + stack[sp - 1]));
-#endif
                         }
 #undef PRT_CHILD_OF
 #if PRT_PREFETCH_LEAF
@@ -530,14 +551,14 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                         const bool h1 = box_f32(b.z, b.w, c.x, c.y, c.z, c.w, rf, tmin32, tbest32, e1) && ch.y != PRT_NO_CHILD;
                         if (h0 && h1) {
                             const bool swap = e1 < e0;
-                            if (sp < PRT_SAH_STACK) stack[sp++] = swap ? ch.x : ch.y; else overflow = true;
+                            PRT_PUSH(swap ? ch.x : ch.y);
                             cur = swap ? ch.y : ch.x;
                         } else if (h0) {
                             cur = ch.x;
                         } else if (h1) {
                             cur = ch.y;
                         } else {
-                            cur = sp > 0 ? stack[--sp] : PRT_DONE;
+                            cur = sp > 0 ? PRT_POP() : PRT_DONE;
                         }
                     }
                 }
@@ -567,7 +588,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                         tbest32 = __double2float_ru(t);
                     }
                 }
-                cur = (done || sp == 0) ? PRT_DONE : stack[--sp];
+                cur = (done || sp == 0) ? PRT_DONE : PRT_POP();
             }
             if (cur == PRT_DONE && has_ray && !ANY && hit.slot >= 0 && on_boundary(hit.alpha, hit.beta)) recheck = true;
             const unsigned walking = __ballot_sync(FULL, has_ray && cur != PRT_DONE);
@@ -577,6 +598,8 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
 #endif
     }
     pol.finish();
+#undef PRT_PUSH
+#undef PRT_POP
 }
 
 }  // namespace prt

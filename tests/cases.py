@@ -36,9 +36,28 @@ def debug():
 SCENES = {"tiny": tiny, "cornell": cornell_small, "veach": veach_small, "bathroom": bathroom_small}
 
 
-def ray_batch(sc, n_random=3000, cam_w=40, cam_h=30, seed=2):
+FAR_SCALE, FAR_OFFSET = 1.0e4, 1.0e6
+
+
+def far():
+    """cornell_small scaled by 1e4 and moved to (1e6, 1e6, 1e6): |o| / extent ~ 50, coordinates carry ~2e-10 of
+    absolute rounding. The adversarial rays of ray_batch (vertices, edge midpoints, in-plane, axis-parallel) are
+    rebuilt from the TRANSFORMED vertices, so they still aim at the stored vertex bits. Pins on_boundary
+    (pooraytracer_b200/csrc/traverse.cuh) away from unit scale (VERDICT r1, weak #2)."""
+    sc = cornell_small()
+    sc.name = "far"
+    sc.vertices = sc.vertices * FAR_SCALE + FAR_OFFSET
+    cam = dict(sc.camera)
+    cam["eye"] = tuple(np.array(cam["eye"]) * FAR_SCALE + FAR_OFFSET)
+    cam["look_at"] = tuple(np.array(cam["look_at"]) * FAR_SCALE + FAR_OFFSET)
+    sc.camera = cam
+    return sc
+
+
+def ray_batch(sc, n_random=3000, cam_w=40, cam_h=30, seed=2, scale=1.0, offset=0.0):
     """random rays + pixel-centre camera rays + adversarial rays (axis-parallel directions with exact
-    zeros, rays aimed at vertices and at edge midpoints, rays in triangle planes)."""
+    zeros, rays aimed at vertices and at edge midpoints, rays in triangle planes). scale / offset move the
+    fixed-coordinate axis-parallel rays with a transformed scene (far())."""
     o1, d1 = scenes.random_rays(sc, n_random, seed=seed)
     o2, d2 = scenes.camera_rays(sc.camera, cam_w, cam_h)
     v = sc.vertices.reshape(-1, 3, 3)
@@ -61,9 +80,22 @@ def ray_batch(sc, n_random=3000, cam_w=40, cam_h=30, seed=2):
     e = v[pick[:50], 1] - v[pick[:50], 0]
     o7 = v[pick[:50], 0] - 2.0 * e
     d7 = e
+    o4, o5, o6 = (x * scale + offset for x in (o4, o5, o6))
+    d4, d5, d6 = (x * scale for x in (d4, d5, d6))
     o = np.concatenate([o1, o2, o3, o4, o5, o6, o7])
     d = np.concatenate([d1, d2, d3, d4, d5, d6, d7])
     return np.ascontiguousarray(o), np.ascontiguousarray(d)
+
+
+def rays_for(key):
+    """(scene, origins, directions) of the ray fixture tests/golden/rays_<key>.npz"""
+    if key == "ties":
+        return tie_scene(), *tie_rays()
+    if key == "far":
+        sc = far()
+        return sc, *ray_batch(sc, scale=FAR_SCALE, offset=FAR_OFFSET)
+    sc = SCENES[key]()
+    return sc, *ray_batch(sc)
 
 
 def tie_scene():

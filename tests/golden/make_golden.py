@@ -68,10 +68,12 @@ def main():
             render_fixture(name)
         return
     tag = ol.PER_TRIANGLE_MATERIAL | ol.UV_TAG
-    for key, make in list(cases.SCENES.items()) + [("ties", cases.tie_scene)]:
-        sc = make()
+    only = sys.argv[2:] if len(sys.argv) > 2 and sys.argv[1] == "rays" else None  # e.g. `make_golden.py rays far`
+    for key in list(cases.SCENES) + ["ties", "far"]:
+        if only is not None and key not in only:
+            continue
+        sc, o, d = cases.rays_for(key)
         R = ol.OracleScene("ref", sc, tag)
-        o, d = cases.tie_rays() if key == "ties" else cases.ray_batch(sc)
         prim, t, a, b = R.trace_closest(o, d, 1e-4, np.inf)
         rank, lo = R.reference_order()
         out = dict(prim=prim, t=t, alpha=a, beta=b, world_rank=rank, light_order=lo)
@@ -88,6 +90,8 @@ def main():
         np.savez_compressed(os.path.join(HERE, f"rays_{key}.npz"), **out)
         print("rays", key, len(prim), int((prim >= 0).sum()), "hits")
         R.close()
+    if only is not None:
+        return
 
     # materials + textures on the tiny scene (every material type, one texture of each channel count
     # lives in the bathroom scene)

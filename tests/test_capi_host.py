@@ -23,7 +23,7 @@ def test_every_declared_symbol_is_exported(built):
     for name in sorted(declared):
         assert hasattr(lib, name), f"{name} declared in include/prt_b200.h but not exported"
     assert declared == set(capi.PROTOTYPES), "ctypes mirror out of sync with the header"
-    assert lib.prt_abi_version() == 1
+    assert lib.prt_abi_version() == 2
 
 
 def test_struct_sizes_match_header(built):
@@ -31,7 +31,7 @@ def test_struct_sizes_match_header(built):
     assert C.sizeof(capi.PrtMaterial) == 8 + 8 * (3 + 3 + 1 + 3 + 2 + 3 + 3)
     assert C.sizeof(capi.PrtCamera) == 8 + 8 * 10
     assert C.sizeof(capi.PrtRenderParams) == 24 + 8 * 5
-    assert C.sizeof(capi.PrtStats) == 8 * 6 + 8 * 4 + 8 + 16 + 8
+    assert C.sizeof(capi.PrtStats) == 8 * 6 + 8 * 4 + 8 + 16 + 8 + 8
 
 
 @pytest.mark.parametrize("key", ["tiny", "cornell", "veach", "bathroom", "ties"])

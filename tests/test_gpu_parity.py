@@ -27,13 +27,11 @@ def gold(name):
 
 
 def scene_and_rays(key):
-    sc = cases.tie_scene() if key == "ties" else cases.SCENES[key]()
-    o, d = cases.tie_rays() if key == "ties" else cases.ray_batch(sc)
-    return sc, o, d
+    return cases.rays_for(key)
 
 
 @pytest.mark.parametrize("accel", ACCELS)
-@pytest.mark.parametrize("key", ["tiny", "cornell", "veach", "bathroom", "ties"])
+@pytest.mark.parametrize("key", ["tiny", "cornell", "veach", "bathroom", "ties", "far"])
 def test_closest_hit_bit_exact_vs_reference_golden(gpu_ctx, key, accel):
     sc, o, d = scene_and_rays(key)
     g = gold(f"rays_{key}.npz")

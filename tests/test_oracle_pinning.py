@@ -19,12 +19,10 @@ def gold(name):
 
 
 def scene_and_rays(key):
-    sc = cases.tie_scene() if key == "ties" else cases.SCENES[key]()
-    o, d = cases.tie_rays() if key == "ties" else cases.ray_batch(sc)
-    return sc, o, d
+    return cases.rays_for(key)
 
 
-@pytest.mark.parametrize("key", ["tiny", "cornell", "veach", "bathroom", "ties"])
+@pytest.mark.parametrize("key", ["tiny", "cornell", "veach", "bathroom", "ties", "far"])
 def test_port_closest_hit_matches_reference_golden(built, key):
     sc, o, d = scene_and_rays(key)
     g = gold(f"rays_{key}.npz")
