@@ -271,6 +271,10 @@ int prt_resolve_device(prt_scene* scene, const double* rgb_device, int32_t width
 /* Same with the radiance image in host memory (the colorAttachment a caller kept). */
 int prt_resolve(prt_scene* scene, const double* rgb, int32_t width, int32_t height, uint8_t* rgb8,
                 float* rgb32f);
+/* Host-side introspection (no GPU needed): out254[k - 1] = the smallest linear value whose 8-bit code is k,
+ * k = 1..254, found with the libm call of Camera::LinearToSRGB (Camera.cpp:216-221) — the table the resolve
+ * kernel quantises by, so that its bytes are the reference's for every double. */
+int prt_resolve_thresholds(double* out254);
 
 /* ---- scene files: replaces Model::Model + Camera::SetViewParametersByXmlFile -------------------
  * Host-only (no GPU needed). Reads <dir>/<name>.obj, the .mtl it names, <dir>/<name>.xml (camera +

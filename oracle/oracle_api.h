@@ -82,6 +82,8 @@ ORACLE_DECLARE(ref)
 ORACLE_DECLARE(orc)
 /* ref only: value of AABB::empty as initialised in this build (static-init-order probe) */
 int ref_aabb_empty(double* out6);
+/* ref only: Camera::WriteColorAttachment (Camera.cpp:279-331) on a caller-supplied W x H x 3 float64 image */
+int ref_write_color_attachment(const double* rgb, int32_t width, int32_t height, const char* png_path, int write_hdr);
 #ifdef __cplusplus
 }
 #endif

@@ -283,6 +283,20 @@ int ref_aabb_empty(double* out6) {
     return 0;
 }
 
+/* The reference's output stage, untouched: Camera::WriteColorAttachment (Camera.cpp:279-331) on a caller-supplied
+ * colorAttachment — writes <png_path> through stbi_write_png and, with write_hdr, <png_path minus extension>.hdr
+ * through stbi_write_hdr. The golden bytes of tests/golden/output_stage.npz come from here. */
+int ref_write_color_attachment(const double* rgb, int32_t width, int32_t height, const char* png_path, int write_hdr) {
+    if (!rgb || !png_path || width < 1 || height < 1) return PRT_ERR_INVALID_ARGUMENT;
+    Camera cam;
+    cam.imageWidth = width;
+    cam.imageHeight = height;
+    cam.colorAttachment.resize((size_t)width * height);
+    for (size_t i = 0; i < (size_t)width * height; ++i) cam.colorAttachment[i] = color(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
+    cam.WriteColorAttachment(std::string(png_path), write_hdr != 0);
+    return 0;
+}
+
 int ref_scene_create(const prt_scene_desc* d, const char* const* texture_paths, int flags,
                      void** out) {
     if (!d || !out || d->n_triangles < 0 || d->n_meshes < 0) return PRT_ERR_INVALID_ARGUMENT;

@@ -152,6 +152,7 @@ PROTOTYPES = {
     "prt_render_device": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p, C.c_void_p]),
     "prt_resolve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "prt_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "prt_resolve_thresholds": (C.c_int, [C.c_void_p]),
     "prt_set_counters": (C.c_int, [C.c_void_p, C.c_int]),
     "prt_get_stats": (C.c_int, [C.c_void_p, C.POINTER(PrtStats)]),
     "prt_synchronize": (C.c_int, [C.c_void_p]),

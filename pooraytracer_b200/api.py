@@ -322,6 +322,15 @@ class Scene:
         _check(self.lib, self.lib.prt_resolve_device(self.handle, C.c_void_p(device_ptr), width, height, _ptr(rgb8), _ptr(f32)))
         return rgb8, f32
 
+    def resolve(self, rgb: np.ndarray, want_float=True):
+        """prt_resolve: host float64 [H, W, 3] -> (uint8 [H, W, 3], float32 [H, W, 3])"""
+        rgb = np.ascontiguousarray(rgb, dtype=np.float64)
+        h, w, _ = rgb.shape
+        rgb8 = np.empty((h, w, 3), dtype=np.uint8)
+        f32 = np.empty((h, w, 3), dtype=np.float32) if want_float else None
+        _check(self.lib, self.lib.prt_resolve(self.handle, _ptr(rgb), w, h, _ptr(rgb8), _ptr(f32)))
+        return rgb8, f32
+
     def set_counters(self, enable: bool):
         _check(self.lib, self.lib.prt_set_counters(self.handle, 1 if enable else 0))
 

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -114,6 +115,7 @@ struct prt_scene {
     DevBuf<double> s_rgb;
     DevBuf<uint8_t> s_rgb8;
     DevBuf<float> s_rgb32f;
+    DevBuf<double> d_thr; /* [254] quantiser thresholds of the output stage (resolve_thresholds) */
 
     /* wavefront pool */
     DevBuf<PathRec> p_rec;
@@ -229,6 +231,41 @@ PathBuffers path_buffers(prt_scene* s) {
     pb.hist = s->p_hist.p; pb.cursor = s->p_cursor.p;
     pb.counters = s->count_visits ? s->d_counters.p : nullptr;
     return pb;
+}
+
+/* The reference's 8-bit quantiser (Camera.cpp:216-221,297-300) with the reference's own libm call */
+inline int quantise_srgb8(double c) {
+    if (c != c) c = 0.0;
+    double s = c <= 0.0031308 ? 12.92 * c : 1.055 * std::pow(c, (1. / 2.4)) - 0.055;
+    s = s < 0.0 ? 0.0 : (s > 0.9999 ? 0.9999 : s); /* Interval::Clamp */
+    return (int)(uint8_t)(s * 255);
+}
+/* thr[k - 1] = the smallest double whose byte is >= k, k = 1..254, by bisection over the bit patterns of the
+ * non-negative doubles (ordered like unsigned integers). Monotonicity of the quantiser is what makes "count the
+ * thresholds reached" equal to it; the 64 neighbours on either side of every threshold are verified here, and
+ * tests/test_gpu_parity.py holds the bytes the compiled reference wrote for the same neighbourhoods. */
+const std::vector<double>& resolve_thresholds() {
+    static std::vector<double> thr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        thr.resize(254);
+        auto value = [](uint64_t bits) { double v; std::memcpy(&v, &bits, 8); return v; };
+        uint64_t one_bits; { const double one = 1.0; std::memcpy(&one_bits, &one, 8); }
+        for (int k = 1; k <= 254; ++k) {
+            uint64_t lo = 0, hi = one_bits; /* q(lo) = 0 < k <= 254 = q(1.0) */
+            while (hi - lo > 1) {
+                const uint64_t mid = lo + (hi - lo) / 2;
+                if (quantise_srgb8(value(mid)) >= k) hi = mid; else lo = mid;
+            }
+            for (int j = 1; j <= 64; ++j) /* monotone around the step, or the comparison form would be wrong */
+                if (quantise_srgb8(value(hi + j)) < k || (hi > (uint64_t)j && quantise_srgb8(value(hi - j)) >= k)) {
+                    std::fprintf(stderr, "[prt] resolve_thresholds: quantiser not monotone near byte %d\n", k);
+                    std::abort();
+                }
+            thr[k - 1] = value(hi);
+        }
+    });
+    return thr;
 }
 
 /* Camera::Initialize, Source/Camera.cpp:75-106 (host libm tan, the function the reference calls) */
@@ -754,7 +791,8 @@ int prt_resolve_device(prt_scene* s, const double* rgb_device, int32_t width, in
     cudaStream_t st = s->ctx->stream;
     if (rgb8) CUDA_TRY(s->s_rgb8.ensure(n));
     if (rgb32f) CUDA_TRY(s->s_rgb32f.ensure(n));
-    launch_resolve(rgb_device, (int64_t)width * height, rgb8 ? s->s_rgb8.p : nullptr, rgb32f ? s->s_rgb32f.p : nullptr, st);
+    if (!s->d_thr.p) CUDA_TRY(s->d_thr.upload(resolve_thresholds(), st));
+    launch_resolve(rgb_device, (int64_t)width * height, s->d_thr.p, rgb8 ? s->s_rgb8.p : nullptr, rgb32f ? s->s_rgb32f.p : nullptr, st);
     CUDA_TRY(cudaGetLastError());
     if (rgb8) CUDA_TRY(cudaMemcpyAsync(rgb8, s->s_rgb8.p, n, cudaMemcpyDeviceToHost, st));
     if (rgb32f) CUDA_TRY(cudaMemcpyAsync(rgb32f, s->s_rgb32f.p, n * sizeof(float), cudaMemcpyDeviceToHost, st));
@@ -770,6 +808,13 @@ int prt_resolve(prt_scene* s, const double* rgb, int32_t width, int32_t height, 
     CUDA_TRY(s->s_rgb.ensure(n));
     CUDA_TRY(cudaMemcpyAsync(s->s_rgb.p, rgb, n * sizeof(double), cudaMemcpyHostToDevice, s->ctx->stream));
     return prt_resolve_device(s, s->s_rgb.p, width, height, rgb8, rgb32f);
+}
+
+int prt_resolve_thresholds(double* out254) {
+    if (!out254) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_resolve_thresholds: null argument");
+    const std::vector<double>& t = resolve_thresholds();
+    std::copy(t.begin(), t.end(), out254);
+    return PRT_OK;
 }
 
 int prt_get_stats(const prt_scene* cs, prt_stats* out) {

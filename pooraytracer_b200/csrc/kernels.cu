@@ -857,20 +857,30 @@ __global__ void k_pass_stats(const BounceCtrl* __restrict__ ctrl, int n_bounces,
 }
 
 /* Camera::WriteColorAttachment's pixel loop: NaN scrub, sRGB OETF (Camera.cpp:216-221), clamp to
- * [0, 0.9999] then *255 truncated (:297-300); float32 copy of the scrubbed linear value (:308-325) */
-__device__ __forceinline__ double linear_to_srgb(double c) {
-    if (c <= 0.0031308) return 12.92 * c;
-    return 1.055 * pow(c, (1. / 2.4)) - 0.055;
-}
-__global__ void __launch_bounds__(256) k_resolve(const double* __restrict__ rgb, int64_t n, uint8_t* __restrict__ rgb8, float* __restrict__ rgb32f) {
+ * [0, 0.9999] then *255 truncated (:297-300); float32 copy of the scrubbed linear value (:308-325).
+ *
+ * The byte is NOT computed with CUDA's pow: it differs from glibc's in the last ulp, and an ulp at one of the 254
+ * places where trunc(clamp(LinearToSRGB(c)) * 255) steps is a different byte. The quantiser is monotone in c, so
+ * the host finds, once, the smallest double that yields each byte value k = 1..254 with the very libm call the
+ * reference makes (capi.cu: resolve_thresholds, bisection over the bit patterns), and the kernel counts how many of
+ * those thresholds c has reached: byte-for-byte the reference's PNG payload (tests/golden/output_stage.npz). */
+__global__ void __launch_bounds__(256) k_resolve(const double* __restrict__ rgb, int64_t n, const double* __restrict__ thr, uint8_t* __restrict__ rgb8,
+                                                 float* __restrict__ rgb32f) {
+    __shared__ double s_thr[256];
+    s_thr[threadIdx.x] = threadIdx.x < 254 ? thr[threadIdx.x] : (double)INFINITY;
+    __syncthreads();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         double c = rgb[i];
         if (c != c) c = 0.0;
         if (rgb32f) rgb32f[i] = (float)c;
         if (rgb8) {
-            double s = linear_to_srgb(c);
-            s = s < 0.0 ? 0.0 : (s > 0.9999 ? 0.9999 : s); /* Interval::Clamp */
-            rgb8[i] = (uint8_t)(s * 255);
+            int lo = 0, hi = 254; /* the byte = number of thresholds <= c */
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (c >= s_thr[mid - 1]) lo = mid;
+                else hi = mid - 1;
+            }
+            rgb8[i] = (uint8_t)lo;
         }
     }
 }
@@ -1052,10 +1062,10 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     return launches;
 }
 
-void launch_resolve(const double* rgb, int64_t npix, uint8_t* rgb8, float* rgb32f, cudaStream_t st) {
+void launch_resolve(const double* rgb, int64_t npix, const double* thresholds, uint8_t* rgb8, float* rgb32f, cudaStream_t st) {
     const int64_t n = npix * 3;
     if (n <= 0) return;
-    k_resolve<<<(unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8), 256, 0, st>>>(rgb, n, rgb8, rgb32f);
+    k_resolve<<<(unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8), 256, 0, st>>>(rgb, n, thresholds, rgb8, rgb32f);
 }
 
 }  // namespace prt

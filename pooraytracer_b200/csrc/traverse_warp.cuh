@@ -55,7 +55,7 @@ namespace prt {
  * the 10 M-triangle meshes below 30) spill to a local array, so depth is never lost; beyond PRT_SAH_STACK the
  * ray goes to the reference-order walk as before. */
 #ifndef PRT_SMEM_STACK
-#define PRT_SMEM_STACK 16
+#define PRT_SMEM_STACK 8
 #endif
 #define PRT_TRAVERSE_BLOCK 128 /* threads per block of every kernel that walks the tree */
 #define PRT_SMEM_STACK_WORDS (((PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) > 0 ? (PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) : 1) * PRT_TRAVERSE_BLOCK)

@@ -59,8 +59,56 @@ def cook_fixtures():
         render_fixture(name)
 
 
+def ref_output_stage(img):
+    """(rgb8 [H,W,3], raw .hdr file bytes) that the reference's Camera::WriteColorAttachment writes for img"""
+    import ctypes as C
+    import tempfile
+    import imgutil
+    lib = ol.OracleLib("ref").lib
+    img = np.ascontiguousarray(img, dtype=np.float64)
+    h, w, _ = img.shape
+    with tempfile.TemporaryDirectory(prefix="prt_out_") as d:
+        path = os.path.join(d, "frame.png")
+        rc = lib.ref_write_color_attachment(img.ctypes.data_as(C.c_void_p), C.c_int32(w), C.c_int32(h), path.encode(), C.c_int(1))
+        assert rc == 0
+        return imgutil.png_rgb8(open(path, "rb").read()), open(os.path.join(d, "frame.hdr"), "rb").read()
+
+
+def output_stage_fixture():
+    """f2 (SURVEY 8f): the bytes Camera::WriteColorAttachment (Camera.cpp:279-331) produces. The 254 places where
+    the 8-bit quantiser steps are located by bisection THROUGH the reference (each probe is a PNG it wrote), then
+    the fixture holds every double within 6 ulps of each step, the special values, and a noisy HDR-range frame."""
+    k = np.arange(1, 255)
+    lo = np.zeros(254, np.uint64)
+    hi = np.full(254, np.float64(1.0).view(np.uint64))
+    while (hi - lo > 1).any():
+        mid = lo + (hi - lo) // 2
+        img = np.zeros((1, 256, 3)); img[0, :254, 0] = mid.view(np.float64)
+        q = ref_output_stage(img)[0][0, :254, 0].astype(int)
+        up = q >= k
+        hi = np.where(up & (hi - lo > 1), mid, hi)
+        lo = np.where(~up & (hi - lo > 1), mid, lo)
+    steps = hi
+    near = (steps[:, None].astype(np.int64) + np.arange(-6, 7)[None, :]).astype(np.uint64).view(np.float64).ravel()
+    special = np.array([np.nan, -np.nan, np.inf, -np.inf, -1.0, -0.0, 0.0, 5e-324, 1e-300, 0.0031308, np.nextafter(0.0031308, 1), np.nextafter(0.0031308, 0),
+                        0.5, 0.9999, 1.0, np.nextafter(1.0, 2), 5.0, 17.0, 1e300, -1e-300, 2.0 ** -130, 3.5e38, 1e39])
+    noise = np.exp(cases.hash_uniform(3 * 64 * 48, 21, 1) * 14.0 - 10.0)  # 4.5e-5 .. 55
+    vals = np.concatenate([near, special, noise])
+    w = 96
+    h = -(-len(vals) // (3 * w))
+    img = np.zeros(h * w * 3)
+    img[:len(vals)] = vals
+    img = img.reshape(h, w, 3)
+    with np.errstate(all="ignore"):
+        rgb8, hdr = ref_output_stage(img)
+    np.savez_compressed(os.path.join(HERE, "output_stage.npz"), image=img, rgb8=rgb8, hdr_file=np.frombuffer(hdr, np.uint8), steps=steps.view(np.float64))
+    print("output_stage", img.shape, "steps", steps.view(np.float64)[[0, 1, 127, 253]], "bytes used", len(np.unique(rgb8)))
+
+
 def main():
     assert ol.available("ref"), "build oracle/_ref first (make -C oracle ref)"
+    if len(sys.argv) > 1 and sys.argv[1] == "output":
+        return output_stage_fixture()
     if len(sys.argv) > 1 and sys.argv[1] == "cook":
         return cook_fixtures()
     if len(sys.argv) > 1 and sys.argv[1] == "debug":  # DebugMaterial renders only (SURVEY 8 f4)
@@ -117,6 +165,7 @@ def main():
         if not name.startswith("cook"):
             render_fixture(name)
     cook_fixtures()
+    output_stage_fixture()
 
 
 if __name__ == "__main__":

@@ -111,3 +111,45 @@ def test_product_never_touches_the_oracle():
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "oracle_lib" not in txt and "libprt_oracle" not in txt and "libprt_ref" not in txt, f
                 assert "/root/reference" not in txt or f.endswith((".cpp", ".cu", ".cuh", ".h")), f
+
+
+def test_resolve_thresholds_are_the_reference_quantiser_steps(built):
+    """f2: the 254 steps of trunc(clamp(LinearToSRGB(c), 0, 0.9999) * 255) (Camera.cpp:216-221,297-300). The library
+    finds them on the host with glibc's pow; tests/golden/output_stage.npz holds the steps located by bisection
+    through PNGs the compiled reference wrote. Bit-equal, all 254."""
+    from pooraytracer_b200 import _capi
+    lib = _capi.load_library()
+    thr = np.zeros(254)
+    assert lib.prt_resolve_thresholds(thr.ctypes.data_as(C.c_void_p)) == 0
+    g = np.load(os.path.join(ROOT, "tests", "golden", "output_stage.npz"))
+    assert np.array_equal(thr, g["steps"])
+    assert (np.diff(thr) > 0).all() and thr[0] > 0 and thr[-1] < 1
+
+
+def test_hdr_decoder_reads_the_reference_file():
+    """tests/imgutil.hdr_rgbe on the file stbi_write_hdr produced (run-length scanlines): mantissas / exponents
+    reproduce float32(image) to RGBE precision"""
+    import imgutil
+    g = np.load(os.path.join(ROOT, "tests", "golden", "output_stage.npz"))
+    rgbe = imgutil.hdr_rgbe(g["hdr_file"].tobytes())
+    img = np.where(np.isnan(g["image"]), 0.0, g["image"])
+    assert rgbe.shape[:2] == img.shape[:2]
+    with np.errstate(all="ignore"):
+        val = rgbe[..., :3].astype(np.float64) * np.exp2(rgbe[..., 3:4].astype(np.float64) - 136.0)
+        mx = np.max(img.astype(np.float32), axis=-1, keepdims=True).astype(np.float64)
+    ok = np.isfinite(mx[..., 0]) & (mx[..., 0] >= 1e-32)
+    assert ok.sum() > 1000
+    assert (np.abs(val - np.clip(img, 0, None))[ok] <= (mx / 128.0 + 1e-30)[ok[..., None].repeat(1, -1)[..., 0]]).all()
+
+
+def test_hdr_writer_payload_equals_reference(tmp_path):
+    """prt_write_hdr (host code) on float32(golden image): the RGBE quadruples stbi_write_hdr wrote for the reference
+    (Camera.cpp:308-327), including the inf / negative / denormal pixels"""
+    import imgutil
+    from pooraytracer_b200 import api
+    g = np.load(os.path.join(ROOT, "tests", "golden", "output_stage.npz"))
+    with np.errstate(all="ignore"):
+        f32 = np.where(np.isnan(g["image"]), 0.0, g["image"]).astype(np.float32)
+    path = str(tmp_path / "x.hdr")
+    api.write_hdr(path, f32)
+    assert np.array_equal(imgutil.hdr_rgbe(open(path, "rb").read()), imgutil.hdr_rgbe(g["hdr_file"].tobytes()))

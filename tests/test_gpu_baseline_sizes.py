@@ -86,6 +86,20 @@ def test_config0_other_accels_vs_reference_render(gpu_ctx, config0, accel):
     compare_same_streams(img, ref, f"configs[0] accel={accel}")
 
 
+def test_config0_without_primary_hit_reuse_vs_reference_render(gpu_ctx, config0, monkeypatch):
+    """PRT_PRIMARY_REUSE=0: bounce 0 traced per sample (the path PRT_RENDER_PIXEL_JITTER takes) — same image, bit for bit,
+    as with the per-pixel primary-hit table, and the same agreement with the CPU reference"""
+    sc, cam, prm, _, ref = config0
+    s = Scene(gpu_ctx, sc, accel=capi.ACCEL_SAH_BVH4)
+    with_reuse = s.render(cam, prm)
+    rays_reuse = s.stats().extend_rays
+    monkeypatch.setenv("PRT_PRIMARY_REUSE", "0")
+    img = s.render(cam, prm)
+    compare_same_streams(img, ref, "configs[0] no primary reuse")
+    assert np.array_equal(img, with_reuse)
+    assert s.stats().extend_rays - rays_reuse == 15 * 512 * 512  # 16 primary rays per pixel instead of one
+
+
 def test_config0_multi_pass_and_shards_vs_reference_render(gpu_ctx, config0, monkeypatch):
     """the pass splitter (PRT_PASS_PATHS: 16 passes of one sample) and the multi-GPU sample sharding
     (4 shards of 4 samples summed) against the same CPU image"""
