@@ -276,6 +276,34 @@ int prt_resolve(prt_scene* scene, const double* rgb, int32_t width, int32_t heig
  * kernel quantises by, so that its bytes are the reference's for every double. */
 int prt_resolve_thresholds(double* out254);
 
+/* ---- the whole box: 1..8 GPUs behind one handle ------------------------------
+ * Replaces main.cpp:36-52 for a caller that wants every GPU of the node: the scene is replicated (copied, flattened
+ * and uploaded once per GPU, concurrently), Camera::Render's samples are split into contiguous ranges across the GPUs
+ * (the generator is keyed by the absolute sample index, so the union of the shards is the one-GPU image up to the order
+ * of the final FP64 additions), and ONE collective — ncclReduce(sum, double, W*H*3) to devices[0] over NVLink — ends
+ * the render. The library owns the communicator; NCCL is bound at run time and only when n > 1. Used from one host
+ * thread at a time; the library runs one thread of its own per GPU. */
+typedef struct prt_multi prt_multi;
+int prt_multi_create(const int32_t* devices, int32_t n, const prt_scene_desc* desc, const prt_build_opts* opts,
+                     prt_multi** out);
+void prt_multi_destroy(prt_multi* multi);
+int prt_multi_device_count(const prt_multi* multi);
+/* Camera::Render on all GPUs: rgb (host, W*H*3 doubles, may be NULL) is OVERWRITTEN with the reduced image of the sample
+ * range, scaled by 1/samples_per_pixel; the reduced accumulators also stay on devices[0] for prt_multi_resolve. */
+int prt_multi_render(prt_multi* multi, const prt_camera* camera, const prt_render_params* params, double* rgb);
+/* The output stage (Camera.cpp:279-331) on devices[0], on the image of the last prt_multi_render: NaN scrub AFTER the
+ * reduce, as the reference scrubs the final pixel. */
+int prt_multi_resolve(prt_multi* multi, uint8_t* rgb8, float* rgb32f);
+/* Sums of the per-GPU counters of the last call, gpu_ms = the slowest GPU's device time; reduce_ms (may be NULL) = device
+ * time of the collective on devices[0]. */
+int prt_multi_get_stats(const prt_multi* multi, prt_stats* out, double* reduce_ms);
+/* Hittable::Hit over a batch split into contiguous ray ranges, one per GPU; no collective. Host pointers. */
+int prt_multi_trace_closest(prt_multi* multi, int64_t n, const double* origins, const double* directions,
+                            const double* tmin, const double* tmax, int32_t* prim, double* t, double* alpha,
+                            double* beta);
+int prt_multi_trace_any(prt_multi* multi, int64_t n, const double* origins, const double* directions,
+                        const double* tmin, const double* tmax, uint8_t* hit);
+
 /* ---- scene files: replaces Model::Model + Camera::SetViewParametersByXmlFile -------------------
  * Host-only (no GPU needed). Reads <dir>/<name>.obj, the .mtl it names, <dir>/<name>.xml (camera +
  * <light mtlname radiance>), and the map_Kd images, the way Source/Model.cpp:53-394 and

@@ -568,10 +568,8 @@ V3 mat_eval(const Scene& s, const Mat& m, V3 wi, const EvalCtx& c, Rng& rng) {
     switch (m.type) {
         case PRT_MAT_LAMBERTIAN:  // Material.h:128-130
             return tex_or_color(s, m.kd_tex, m.kd, c.uv) * InvPi;
-        case PRT_MAT_PHONG: {  // Material.h:227-248 (draws a number; the stream is not advanced: ORC_DEFINE_UB)
-            uint32_t saved = rng.dim;
+        case PRT_MAT_PHONG: {  // Material.h:227-248: draws a number (Material.h:228) — an ordinary, stream-advancing draw
             double u = rng.RandomDouble();
-            if (rng.mode == ORC_RNG_COUNTER && !rng.script) rng.dim = saved;
             if (u < m.pkd) {
                 if (wi.z <= 0) return v3(0, 0, 0);
                 return tex_or_color(s, m.kd_tex, m.kd, c.uv) * InvPi;

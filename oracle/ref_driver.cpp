@@ -158,8 +158,9 @@ private:
     const Hittable& inner;
 };
 
-// ORC_DEFINE_UB: gives the two undefined spots of the Phong material a defined meaning while the
-// reference's own Scatter/Eval bodies still do all the work.
+// ORC_DEFINE_UB: gives the ONE undefined spot of the Phong material a defined meaning while the reference's own
+// Scatter body still does all the work. (PhoneReflectance::Eval's RandomDouble(), Material.h:228, is NOT undefined: it
+// is an ordinary draw that advances the stream, and it does so here exactly as in the unmodified reference.)
 class PhongDefined : public PhoneReflectance {
 public:
     using PhoneReflectance::PhoneReflectance;
@@ -167,13 +168,6 @@ public:
                  Ray& scatteredRay) const override {
         attenuation = color(0., 0., 0.);  // Camera.cpp:177 leaves it uninitialised
         return PhoneReflectance::Scatter(rayIn, record, attenuation, scatteredRay);
-    }
-    vec3 Eval(const vec3& wi, const MaterialEvalContext& context) const override {
-        ThreadState& t = tls();
-        uint32_t saved = t.dim;
-        vec3 f = PhoneReflectance::Eval(wi, context);
-        if (t.mode == MODE_COUNTER) t.dim = saved;  // Material.h:228 draw: value never matters
-        return f;
     }
 };
 

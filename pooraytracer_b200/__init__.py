@@ -5,6 +5,6 @@ Only what the render hot path needs: `csrc/` (CUDA kernels + the C-ABI library
 procedural scene / ray generators (`scenes`) that stand in for the reference's absent scene files.
 """
 from . import _capi, scenes  # noqa: F401
-from .api import Context, Model, Scene, PrtError, load_image, make_camera, make_params, make_scene_desc, write_hdr, write_png  # noqa: F401
+from .api import Context, Model, MultiScene, Scene, PrtError, load_image, make_camera, make_params, make_scene_desc, write_hdr, write_png  # noqa: F401
 
-__all__ = ["Context", "Model", "Scene", "load_image", "write_png", "write_hdr", "PrtError", "make_camera", "make_params", "make_scene_desc", "scenes"]
+__all__ = ["Context", "Model", "MultiScene", "Scene", "load_image", "write_png", "write_hdr", "PrtError", "make_camera", "make_params", "make_scene_desc", "scenes"]

@@ -156,6 +156,14 @@ PROTOTYPES = {
     "prt_set_counters": (C.c_int, [C.c_void_p, C.c_int]),
     "prt_get_stats": (C.c_int, [C.c_void_p, C.POINTER(PrtStats)]),
     "prt_synchronize": (C.c_int, [C.c_void_p]),
+    "prt_multi_create": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(PrtSceneDesc), C.POINTER(PrtBuildOpts), C.POINTER(C.c_void_p)]),
+    "prt_multi_destroy": (None, [C.c_void_p]),
+    "prt_multi_device_count": (C.c_int, [C.c_void_p]),
+    "prt_multi_render": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p]),
+    "prt_multi_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "prt_multi_get_stats": (C.c_int, [C.c_void_p, C.POINTER(PrtStats), C.POINTER(C.c_double)]),
+    "prt_multi_trace_closest": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 8),
+    "prt_multi_trace_any": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 5),
     "prt_model_load": (C.c_int, [C.c_char_p, C.c_char_p, C.c_uint32, C.POINTER(C.c_void_p)]),
     "prt_model_destroy": (None, [C.c_void_p]),
     "prt_model_desc": (C.POINTER(PrtSceneDesc), [C.c_void_p]),

@@ -338,3 +338,67 @@ class Scene:
         s = capi.PrtStats()
         _check(self.lib, self.lib.prt_get_stats(self.handle, C.byref(s)))
         return s
+
+
+class MultiScene:
+    """prt_multi: one scene replicated on several GPUs of the box, samples sharded, one NCCL reduce (harness mirror of
+    include/prt_b200.h's prt_multi_* calls)."""
+
+    def __init__(self, devices, data, accel: int = capi.ACCEL_SAH_BVH4, max_leaf: int = 0):
+        self.lib = capi.load_library()
+        self.data = data
+        devs = np.ascontiguousarray(list(devices), dtype=np.int32)
+        o = capi.PrtBuildOpts()
+        o.accel = int(accel)
+        o.reserved[0] = int(max_leaf)
+        h = C.c_void_p()
+        if isinstance(data, Model):
+            _check(self.lib, self.lib.prt_multi_create(_ptr(devs), len(devs), C.byref(data.desc), C.byref(o), C.byref(h)))
+        else:
+            desc, keep = make_scene_desc(data)
+            _check(self.lib, self.lib.prt_multi_create(_ptr(devs), len(devs), C.byref(desc), C.byref(o), C.byref(h)))
+            del keep
+        self.handle = h
+        self.n = len(devs)
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.prt_multi_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def render(self, camera: capi.PrtCamera, params: capi.PrtRenderParams, out: np.ndarray | None = None) -> np.ndarray:
+        img = out if out is not None else np.empty((camera.image_height, camera.image_width, 3), dtype=np.float64)
+        _check(self.lib, self.lib.prt_multi_render(self.handle, C.byref(camera), C.byref(params), _ptr(img)))
+        return img
+
+    def resolve(self, width: int, height: int, want_float=True):
+        rgb8 = np.empty((height, width, 3), dtype=np.uint8)
+        f32 = np.empty((height, width, 3), dtype=np.float32) if want_float else None
+        _check(self.lib, self.lib.prt_multi_resolve(self.handle, _ptr(rgb8), _ptr(f32)))
+        return rgb8, f32
+
+    def stats(self):
+        s = capi.PrtStats()
+        ms = C.c_double(0.0)
+        _check(self.lib, self.lib.prt_multi_get_stats(self.handle, C.byref(s), C.byref(ms)))
+        return s, ms.value
+
+    def trace_closest(self, o, d, tmin=1e-4, tmax=np.inf):
+        n, o, d, tmin, tmax = Scene._rays(o, d, tmin, tmax)
+        prim = np.empty(n, dtype=np.int32)
+        t = np.zeros(n); a = np.zeros(n); b = np.zeros(n)
+        _check(self.lib, self.lib.prt_multi_trace_closest(self.handle, n, _ptr(o), _ptr(d), _ptr(tmin), _ptr(tmax),
+                                                          _ptr(prim), _ptr(t), _ptr(a), _ptr(b)))
+        return prim, t, a, b
+
+    def trace_any(self, o, d, tmin=1e-3, tmax=np.inf):
+        n, o, d, tmin, tmax = Scene._rays(o, d, tmin, tmax)
+        hit = np.empty(n, dtype=np.uint8)
+        _check(self.lib, self.lib.prt_multi_trace_any(self.handle, n, _ptr(o), _ptr(d), _ptr(tmin), _ptr(tmax), _ptr(hit)))
+        return hit

@@ -17,6 +17,7 @@
 
 #include "../../include/prt_b200.h"
 #include "bvh_device.h"
+#include "capi_internal.h"
 #include "launch.h"
 #include "scene_host.h"
 
@@ -33,12 +34,6 @@ int fail(int code, const std::string& msg) {
 namespace prt {
 int set_error(int code, const std::string& msg) { return fail(code, msg); } /* for scene_io.cpp */
 }
-
-struct prt_context {
-    int device = -1; /* < 0: host-only */
-    cudaStream_t stream = nullptr;
-    int sm_count = 148;
-};
 
 namespace {
 

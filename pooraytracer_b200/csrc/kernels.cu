@@ -534,8 +534,262 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScen
 #ifndef PRT_SHADE_PREFETCH
 #define PRT_SHADE_PREFETCH 1
 #endif
+/* The vertex itself: everything between "this slot holds a hit on a surface of class CLS" and "these are its
+ * shadow ray and its next segment" (Camera.cpp:134-201). prim_hint >= 0: the hit primitive, already known to the
+ * caller (read an iteration ahead so that its TriShade line could be prefetched). */
 template <int CLS, bool PRIMARY>
-__device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort) {
+__device__ __forceinline__ void shade_vertex(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort, int32_t slot,
+                                             bool& want_shadow, bool& want_extend, uint32_t& key_shadow, uint32_t& key_extend) {
+    /* ---- the vertex: hit, incoming ray, throughput, RNG dimension ---- */
+    int32_t prim;
+    double t, alpha, beta;
+    d3 ro, rd, T;
+    uint32_t dim;
+    if (PRIMARY) {
+        const dd4 ph = ld256d(pb.primary + (slot % rc.npix)); /* written by the previous launch: read-only here */
+        t = ph.v[0]; alpha = ph.v[1]; beta = ph.v[2];
+        prim = (int32_t)unpack_lo(ph.v[3]);
+    } else {
+        const dd4 s4 = ld256g(rec_sector(pb, slot, 4));
+        t = s4.v[0]; alpha = s4.v[1]; beta = s4.v[2];
+        prim = (int32_t)unpack_lo(s4.v[3]);
+    }
+    if (PRIMARY || bounce == 0) {
+        /* bounce 0: the camera ray and T = 1 are recomputed instead of being written by the extend stage and
+         * read back; the stream starts at dimension 0 (2 after the jitter draws) */
+        camera_ray(rc, slot, ro, rd);
+        T = mk3(1.0, 1.0, 1.0);
+        dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u;
+    } else {
+        const dd4 s0 = ld256g(rec_sector(pb, slot, 0)), s1 = ld256g(rec_sector(pb, slot, 1)), s2 = ld256g(rec_sector(pb, slot, 2));
+        ro = mk3(s0.v[0], s0.v[1], s0.v[2]);
+        rd = mk3(s0.v[3], s1.v[0], s1.v[1]);
+        T = mk3(s1.v[2], s1.v[3], s2.v[0]);
+        dim = unpack_lo(s2.v[1]) & 0x7fffffffu;
+    }
+    const TriShade* __restrict__ sh = S.shade + prim;
+    const DevMaterial m = S.materials[sh->material];
+    /* the HitRecord of Triangle::Hit (Triangle.cpp:76-80,111) */
+    Surface s;
+    s.position = ro + rd * t;
+    s.uv = (1. - alpha - beta) * mk2(sh->uv[0], sh->uv[1]) + alpha * mk2(sh->uv[2], sh->uv[3]) + beta * mk2(sh->uv[4], sh->uv[5]);
+    s.tangent = mk3(sh->tangent[0], sh->tangent[1], sh->tangent[2]);
+    const d3 gn = mk3(sh->normal[0], sh->normal[1], sh->normal[2]);
+    s.front = dot(rd, gn) < 0.; /* SetFaceNormal, Hittable.cpp:8-13 */
+    s.normal = s.front ? gn : -gn;
+    const d3 wo = world_to_local(-rd, s);
+
+    Rng rng;
+    rng.seed = stream_seed(rc.rng_key, (uint32_t)(slot % rc.npix), (uint32_t)(rc.sample_first + slot / rc.npix));
+    rng.dim = dim;
+
+    /* ---- next-event estimation (Camera.cpp:137-174) ---- */
+    d3 lp = mk3(0.0, 0.0, 0.0), sc = mk3(0.0, 0.0, 0.0);
+    if (rc.sample_lights && !m.skip_light_sampling) {
+        const double u0 = rng.next(), u1 = rng.next(), u2 = rng.next(), u3 = rng.next();
+        LightSample ls;
+        sample_lights(S, s.position, u0, u1, u2, u3, ls, (rc.flags & PRT_RENDER_UNBIASED_LIGHT_PICK) != 0);
+        const d3 to_light = ls.position - s.position;
+        const d3 light_dir = normalize(to_light);
+        const double distance = length(to_light);
+        if (dot(s.normal, light_dir) > 0.0 && ls.front) {
+            const DevMaterial* lm = S.materials + ls.material;
+            const d3 emission = mk3(lm->emission[0], lm->emission[1], lm->emission[2]);
+            const d3 local_wi = world_to_local(light_dir, s);
+            const d3 local_ln = world_to_local(ls.normal, s);
+            const d3 fr = material_eval(S, m, local_wi, wo, s.uv, rng);
+            const double cos_theta = local_wi.z;
+            const double cos_theta_bar = dot(local_ln, -local_wi);
+            d3 direct = emission * fr * cos_theta * cos_theta_bar / (distance * distance) / ls.pdf;
+            if ((rc.flags & PRT_RENDER_MIS) && (CLS == CLS_LAMBERT || (CLS == CLS_PHONG && m.pkd == 1.0))) {
+                /* balance heuristic against the cosine lobe's density for the same direction */
+                const double pl = ls.pdf * (distance * distance) / cos_theta_bar;
+                const double pbsdf = cos_theta * PRT_INV_PI;
+                direct = direct * (pl / (pl + pbsdf));
+            }
+            /* the shadow ray is stored as its target: k_shadow recomputes light_dir and distance from
+             * (lp, o = s.position) with the functions used above */
+            lp = ls.position;
+            sc = T * direct;
+            want_shadow = true;
+            if (sort) key_shadow = ray_key(rc.key_lo, rc.key_scale, s.position, light_dir);
+        }
+    }
+    /* ---- Russian roulette + BSDF sampling (Camera.cpp:176-201) ---- */
+    d3 out_dir = rd, Tn = T;
+    uint32_t dimflags = dim;
+    float prev_pdf = 0.f;
+    if (rng.next() < rc.rr) {
+        d3 att, sd;
+        bool scattered = true;
+        double cosine_pdf = 0.0;
+        if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, sd, cosine_pdf);
+        else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, sd, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
+        else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, sd);
+        else scatter_mirror(s, wo, att, sd);
+        /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
+        if (scattered && bounce < rc.max_depth) {
+            out_dir = sd;
+            Tn = T * att / rc.rr;
+            dimflags = rng.dim | (m.skip_light_sampling ? 0x80000000u : 0u);
+            prev_pdf = (rc.flags & PRT_RENDER_MIS) ? (float)cosine_pdf : 0.f;
+            want_extend = true;
+            if (sort) key_extend = ray_key(rc.key_lo, rc.key_scale, s.position, out_dir);
+        }
+    }
+    /* ---- the record: whole sectors, only those a later stage reads ---- */
+    if (want_extend || want_shadow) st256g(rec_sector(pb, slot, 0), s.position.x, s.position.y, s.position.z, out_dir.x);
+    if (want_extend) st256g(rec_sector(pb, slot, 1), out_dir.y, out_dir.z, Tn.x, Tn.y);
+    if (want_extend || want_shadow) st256g(rec_sector(pb, slot, 2), Tn.z, pack2(dimflags, __float_as_uint(prev_pdf)), lp.x, lp.y);
+    if (want_shadow) st256g(rec_sector(pb, slot, 3), lp.z, sc.x, sc.y, sc.z);
+    if (PRIMARY) lum_set(pb, slot, mk3(0.0, 0.0, 0.0)); /* bounce 0 initialises the radiance of every path */
+}
+
+#ifndef PRT_SHADE_STAGE
+#define PRT_SHADE_STAGE 1 /* 1: persistent warps over contiguous chunks, pushes staged in shared memory; 0: round 1's grid-stride loop */
+#endif
+#ifndef PRT_SHADE_CHUNK_ITERS
+#define PRT_SHADE_CHUNK_ITERS 8
+#endif
+#ifndef PRT_SHADE_AHEAD
+#define PRT_SHADE_AHEAD 0 /* 1: read the next vertex's primitive id an iteration ahead and prefetch its TriShade line into L1.
+                             Measured (profiles/r2_s4_shade_ab.txt): k_shade 23.4 ms with it, 21.3 ms without — the extra load
+                             and its address arithmetic cost more than the hop they hide */
+#endif
+#define PRT_SHADE_CHUNK (32 * PRT_SHADE_CHUNK_ITERS)
+/* shared memory of one shade block (4 warps): per warp two staged queues (shadow, extend) of one chunk's worth of
+ * entries, plus their ray-binning keys */
+#define PRT_SHADE_STAGE_WORDS (PRT_SHADE_STAGE ? 4 * (2 * PRT_SHADE_CHUNK + PRT_SHADE_CHUNK) : 1)
+
+/* Queue position q of class CLS -> the path slot it names (-1 past the end). PRIMARY: the queue holds pixels and
+ * position q means sample q / nq of pixel queue[q % nq] (sample-major: neighbouring positions, neighbouring records). */
+template <bool PRIMARY>
+__device__ __forceinline__ int32_t shade_entry(const int32_t* queue, int32_t nq, int32_t n, int32_t npix, int64_t q) {
+    if (q >= (int64_t)n) return -1;
+    if (PRIMARY) {
+        const int32_t s = (int32_t)q / nq;
+        return s * npix + __ldcg(queue + ((int32_t)q - s * nq));
+    }
+    return __ldcg(queue + q);
+}
+
+#if PRT_SHADE_STAGE
+/* One warp = one contiguous chunk of PRT_SHADE_CHUNK queue positions at a time (one atomic on the class cursor per
+ * chunk, issued a chunk ahead). The vertices' pushes go to two per-warp staging arrays in shared memory — positions
+ * from a ballot, no atomics — and are flushed once per chunk: ONE atomicAdd per output queue per 256 vertices instead
+ * of one per 32 (the round-trip of those atomics was 9 % of the stall samples, profiles/r2_s2_shade_hot_sass.txt),
+ * and a chunk's survivors land in the output queue next to each other, in queue order: the records the next
+ * kernels gather stay neighbours (round 1's per-iteration pushes interleaved 2368 warps' groups of ~20). */
+template <int CLS, bool PRIMARY>
+__device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort, int32_t* stage) {
+    const unsigned FULL = 0xffffffffu;
+    BounceCtrl* ctrl = pb.ctrl + bounce;
+    BounceCtrl* next = pb.ctrl + bounce + 1;
+    const int32_t nq = __ldcg(&ctrl->n_mat[CLS]);
+    const int32_t n = PRIMARY ? nq * rc.n_samples : nq;
+    const int32_t* queue = pb.q_mat[CLS]; /* ld.cg: k_tail rewrites the queues inside one launch */
+    int32_t* const q_shadow = pb.q_shadow;
+    int32_t* const q_extend = pb.q_extend[(bounce + 1) & 1];
+    const int lane = lane_id(), warp = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    int32_t* st_s = stage + warp * (3 * PRT_SHADE_CHUNK);
+    int32_t* st_e = st_s + PRT_SHADE_CHUNK;
+    uint16_t* st_ks = reinterpret_cast<uint16_t*>(st_e + PRT_SHADE_CHUNK);
+    uint16_t* st_ke = st_ks + PRT_SHADE_CHUNK;
+    int32_t* cursor = &ctrl->fetch_mat[CLS];
+    /* chunk length: PRT_SHADE_CHUNK_ITERS warp-iterations when the queue is long, fewer when it is not — every warp of
+     * the grid should see at least eight chunks, or the late, short bounces run on a fraction of the machine */
+    const int32_t per_warp = n / (int32_t)(gridDim.x * (blockDim.x >> 5) * 32 * 8);
+    const int K = per_warp < 1 ? 1 : (per_warp < PRT_SHADE_CHUNK_ITERS ? per_warp : PRT_SHADE_CHUNK_ITERS);
+    const int32_t CH = 32 * K;
+    int32_t a_raw = 0;
+    if (lane == 0) a_raw = atomicAdd(cursor, CH);
+    int32_t base = __shfl_sync(FULL, a_raw, 0);
+    if (base >= n) return;
+    if (lane == 0) a_raw = atomicAdd(cursor, CH); /* the chunk after this one */
+    int32_t slot_next = shade_entry<PRIMARY>(queue, nq, n, rc.npix, (int64_t)base + lane);
+    for (;;) {
+        int32_t ns = 0, ne = 0;
+        int32_t base_next = 0;
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            const int32_t slot = slot_next;
+            if (k + 1 < K) {
+                slot_next = shade_entry<PRIMARY>(queue, nq, n, rc.npix, (int64_t)base + (k + 1) * 32 + lane);
+            } else {
+                base_next = __shfl_sync(FULL, a_raw, 0); /* issued a whole chunk ago */
+                slot_next = shade_entry<PRIMARY>(queue, nq, n, rc.npix, (int64_t)base_next + lane);
+            }
+#if PRT_SHADE_PREFETCH
+            if (!PRIMARY && slot_next >= 0) {
+                if (bounce == 0) {
+                    prefetch_l2(rec_sector(pb, slot_next, 4)); /* bounce 0 without reuse reads the hit only */
+                } else {
+                    prefetch_l2(rec_sector(pb, slot_next, 0)); /* 160 B: two 128-byte lines at most */
+                    prefetch_l2(rec_sector(pb, slot_next, 4));
+                }
+            }
+#endif
+#if PRT_SHADE_AHEAD
+            /* the next vertex's primitive id, asked for now (its record line comes along), used at the END of this
+             * iteration to pull that triangle's shading record into L1: the chain slot -> hit -> TriShade -> material
+             * of the next iteration then starts two hops in */
+            int32_t prim_next = -1;
+            if (slot_next >= 0)
+                prim_next = PRIMARY ? __ldg(reinterpret_cast<const int32_t*>(pb.primary + (slot_next % rc.npix)) + 6)
+                                    : __ldcg(reinterpret_cast<const int32_t*>(rec_sector(pb, slot_next, 4)) + 6);
+#endif
+            bool want_shadow = false, want_extend = false;
+            uint32_t key_shadow = 0, key_extend = 0;
+            if (slot >= 0) shade_vertex<CLS, PRIMARY>(S, rc, pb, bounce, sort, slot, want_shadow, want_extend, key_shadow, key_extend);
+#if PRT_SHADE_AHEAD
+            if (prim_next >= 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(S.shade + prim_next));
+#endif
+            __syncwarp();
+            const unsigned ms = __ballot_sync(FULL, want_shadow), me = __ballot_sync(FULL, want_extend);
+            if (want_shadow) {
+                const int at = ns + __popc(ms & lt);
+                st_s[at] = slot;
+                if (sort) { st_ks[at] = (uint16_t)key_shadow; atomicAdd(pb.hist + PRT_KEY_BINS + key_shadow, 1); }
+            }
+            if (want_extend) {
+                const int at = ne + __popc(me & lt);
+                st_e[at] = slot;
+                if (sort) { st_ke[at] = (uint16_t)key_extend; atomicAdd(pb.hist + key_extend, 1); }
+            }
+            ns += __popc(ms);
+            ne += __popc(me);
+            if ((int64_t)base + (k + 1) * 32 >= (int64_t)n && k + 1 < K) { /* the queue ended inside this chunk (warp-uniform) */
+                base_next = n;
+                break;
+            }
+        }
+        __syncwarp();
+        /* flush: one atomic per output queue, then a coalesced copy out of shared memory */
+        int32_t rs = 0, re = 0;
+        if (lane == 0) {
+            if (ns) rs = atomicAdd(&ctrl->n_shadow, ns);
+            if (ne) re = atomicAdd(&next->n_extend, ne);
+        }
+        rs = __shfl_sync(FULL, rs, 0);
+        re = __shfl_sync(FULL, re, 0);
+        for (int i = lane; i < ns; i += 32) {
+            q_shadow[rs + i] = st_s[i];
+            if (sort) pb.key_shadow[rs + i] = st_ks[i];
+        }
+        for (int i = lane; i < ne; i += 32) {
+            q_extend[re + i] = st_e[i];
+            if (sort) pb.key_extend[re + i] = st_ke[i];
+        }
+        __syncwarp();
+        base = base_next;
+        if (base >= n) break;
+        if (lane == 0) a_raw = atomicAdd(cursor, CH);
+    }
+}
+#else
+template <int CLS, bool PRIMARY>
+__device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort, int32_t*) {
     BounceCtrl* ctrl = pb.ctrl + bounce;
     BounceCtrl* next = pb.ctrl + bounce + 1;
     const int32_t nq = __ldcg(&ctrl->n_mat[CLS]);
@@ -577,109 +831,7 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
         }
 #endif
         if (slot >= 0) {
-            /* ---- the vertex: hit, incoming ray, throughput, RNG dimension ---- */
-            int32_t prim;
-            double t, alpha, beta;
-            d3 ro, rd, T;
-            uint32_t dim;
-            if (PRIMARY) {
-                const dd4 ph = ld256d(pb.primary + (slot % rc.npix)); /* written by the previous launch: read-only here */
-                t = ph.v[0]; alpha = ph.v[1]; beta = ph.v[2];
-                prim = (int32_t)unpack_lo(ph.v[3]);
-            } else {
-                const dd4 s4 = ld256g(rec_sector(pb, slot, 4));
-                t = s4.v[0]; alpha = s4.v[1]; beta = s4.v[2];
-                prim = (int32_t)unpack_lo(s4.v[3]);
-            }
-            if (PRIMARY || bounce == 0) {
-                /* bounce 0: the camera ray and T = 1 are recomputed instead of being written by the extend stage and
-                 * read back; the stream starts at dimension 0 (2 after the jitter draws) */
-                camera_ray(rc, slot, ro, rd);
-                T = mk3(1.0, 1.0, 1.0);
-                dim = (rc.flags & PRT_RENDER_PIXEL_JITTER) ? 2u : 0u;
-            } else {
-                const dd4 s0 = ld256g(rec_sector(pb, slot, 0)), s1 = ld256g(rec_sector(pb, slot, 1)), s2 = ld256g(rec_sector(pb, slot, 2));
-                ro = mk3(s0.v[0], s0.v[1], s0.v[2]);
-                rd = mk3(s0.v[3], s1.v[0], s1.v[1]);
-                T = mk3(s1.v[2], s1.v[3], s2.v[0]);
-                dim = unpack_lo(s2.v[1]) & 0x7fffffffu;
-            }
-            const TriShade* __restrict__ sh = S.shade + prim;
-            const DevMaterial m = S.materials[sh->material];
-            /* the HitRecord of Triangle::Hit (Triangle.cpp:76-80,111) */
-            Surface s;
-            s.position = ro + rd * t;
-            s.uv = (1. - alpha - beta) * mk2(sh->uv[0], sh->uv[1]) + alpha * mk2(sh->uv[2], sh->uv[3]) + beta * mk2(sh->uv[4], sh->uv[5]);
-            s.tangent = mk3(sh->tangent[0], sh->tangent[1], sh->tangent[2]);
-            const d3 gn = mk3(sh->normal[0], sh->normal[1], sh->normal[2]);
-            s.front = dot(rd, gn) < 0.; /* SetFaceNormal, Hittable.cpp:8-13 */
-            s.normal = s.front ? gn : -gn;
-            const d3 wo = world_to_local(-rd, s);
-
-            Rng rng;
-            rng.seed = stream_seed(rc.rng_key, (uint32_t)(slot % rc.npix), (uint32_t)(rc.sample_first + slot / rc.npix));
-            rng.dim = dim;
-
-            /* ---- next-event estimation (Camera.cpp:137-174) ---- */
-            d3 lp = mk3(0.0, 0.0, 0.0), sc = mk3(0.0, 0.0, 0.0);
-            if (rc.sample_lights && !m.skip_light_sampling) {
-                const double u0 = rng.next(), u1 = rng.next(), u2 = rng.next(), u3 = rng.next();
-                LightSample ls;
-                sample_lights(S, s.position, u0, u1, u2, u3, ls, (rc.flags & PRT_RENDER_UNBIASED_LIGHT_PICK) != 0);
-                const d3 to_light = ls.position - s.position;
-                const d3 light_dir = normalize(to_light);
-                const double distance = length(to_light);
-                if (dot(s.normal, light_dir) > 0.0 && ls.front) {
-                    const DevMaterial* lm = S.materials + ls.material;
-                    const d3 emission = mk3(lm->emission[0], lm->emission[1], lm->emission[2]);
-                    const d3 local_wi = world_to_local(light_dir, s);
-                    const d3 local_ln = world_to_local(ls.normal, s);
-                    const d3 fr = material_eval(S, m, local_wi, wo, s.uv, rng);
-                    const double cos_theta = local_wi.z;
-                    const double cos_theta_bar = dot(local_ln, -local_wi);
-                    d3 direct = emission * fr * cos_theta * cos_theta_bar / (distance * distance) / ls.pdf;
-                    if ((rc.flags & PRT_RENDER_MIS) && (CLS == CLS_LAMBERT || (CLS == CLS_PHONG && m.pkd == 1.0))) {
-                        /* balance heuristic against the cosine lobe's density for the same direction */
-                        const double pl = ls.pdf * (distance * distance) / cos_theta_bar;
-                        const double pbsdf = cos_theta * PRT_INV_PI;
-                        direct = direct * (pl / (pl + pbsdf));
-                    }
-                    /* the shadow ray is stored as its target: k_shadow recomputes light_dir and distance from
-                     * (lp, o = s.position) with the functions used above */
-                    lp = ls.position;
-                    sc = T * direct;
-                    want_shadow = true;
-                    if (sort) key_shadow = ray_key(rc.key_lo, rc.key_scale, s.position, light_dir);
-                }
-            }
-            /* ---- Russian roulette + BSDF sampling (Camera.cpp:176-201) ---- */
-            d3 out_dir = rd, Tn = T;
-            uint32_t dimflags = dim;
-            float prev_pdf = 0.f;
-            if (rng.next() < rc.rr) {
-                d3 att, sd;
-                bool scattered = true;
-                double cosine_pdf = 0.0;
-                if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, sd, cosine_pdf);
-                else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, sd, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
-                else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, sd);
-                else scatter_mirror(s, wo, att, sd);
-                /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
-                if (scattered && bounce < rc.max_depth) {
-                    out_dir = sd;
-                    Tn = T * att / rc.rr;
-                    dimflags = rng.dim | (m.skip_light_sampling ? 0x80000000u : 0u);
-                    prev_pdf = (rc.flags & PRT_RENDER_MIS) ? (float)cosine_pdf : 0.f;
-                    want_extend = true;
-                    if (sort) key_extend = ray_key(rc.key_lo, rc.key_scale, s.position, out_dir);
-                }
-            }
-            /* ---- the record: whole sectors, only those a later stage reads ---- */
-            if (want_extend || want_shadow) st256g(rec_sector(pb, slot, 0), s.position.x, s.position.y, s.position.z, out_dir.x);
-            if (want_extend) st256g(rec_sector(pb, slot, 1), out_dir.y, out_dir.z, Tn.x, Tn.y);
-            if (want_extend || want_shadow) st256g(rec_sector(pb, slot, 2), Tn.z, pack2(dimflags, __float_as_uint(prev_pdf)), lp.x, lp.y);
-            if (want_shadow) st256g(rec_sector(pb, slot, 3), lp.z, sc.x, sc.y, sc.z);
-            if (PRIMARY) lum_set(pb, slot, mk3(0.0, 0.0, 0.0)); /* bounce 0 initialises the radiance of every path */
+            shade_vertex<CLS, PRIMARY>(S, rc, pb, bounce, sort, slot, want_shadow, want_extend, key_shadow, key_extend);
         }
         __syncwarp();
         {
@@ -705,9 +857,12 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
     }
 }
 
+#endif
+
 template <int CLS, bool PRIMARY>
 __global__ void __launch_bounds__(128, PRT_SHADE_MIN_BLOCKS) k_shade(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sort) {
-    shade_body<CLS, PRIMARY>(S, rc, pb, bounce, sort);
+    __shared__ int32_t stage[PRT_SHADE_STAGE_WORDS];
+    shade_body<CLS, PRIMARY>(S, rc, pb, bounce, sort, stage);
 }
 
 /* NEE visibility (Camera.cpp:143-155). The reference asks for the closest hit on [1e-3, DBL_MAX]
@@ -792,17 +947,18 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScen
  * The barrier after the shadow stage is needed: shadow(b) and extend(b + 1) both update the radiance cells. */
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, 2) k_tail(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int first) {
-    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
+    /* the stages are separated by grid-wide barriers: the traversal stack and the shade staging share one buffer */
+    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS > PRT_SHADE_STAGE_WORDS ? PRT_SMEM_STACK_WORDS : PRT_SHADE_STAGE_WORDS];
     cg::grid_group grid = cg::this_grid();
     VisitCounters cnt = {0, 0, 0, 0, 0};
     for (int b = first; b <= rc.max_depth; ++b) {
         if (b > 0 && __ldcg(&pb.ctrl[b].n_extend) == 0) break; /* uniform: written before the last barrier */
         extend_body<COUNT, WIDE>(S, prim_class, rc, pb, b, 0, cnt, sm_stack);
         grid.sync();
-        if (rc.class_mask & (1 << CLS_LAMBERT)) shade_body<CLS_LAMBERT, false>(S, rc, pb, b, 0);
-        if (rc.class_mask & (1 << CLS_PHONG)) shade_body<CLS_PHONG, false>(S, rc, pb, b, 0);
-        if (rc.class_mask & (1 << CLS_MIRROR)) shade_body<CLS_MIRROR, false>(S, rc, pb, b, 0);
-        if (rc.class_mask & (1 << CLS_COOK)) shade_body<CLS_COOK, false>(S, rc, pb, b, 0);
+        if (rc.class_mask & (1 << CLS_LAMBERT)) shade_body<CLS_LAMBERT, false>(S, rc, pb, b, 0, sm_stack);
+        if (rc.class_mask & (1 << CLS_PHONG)) shade_body<CLS_PHONG, false>(S, rc, pb, b, 0, sm_stack);
+        if (rc.class_mask & (1 << CLS_MIRROR)) shade_body<CLS_MIRROR, false>(S, rc, pb, b, 0, sm_stack);
+        if (rc.class_mask & (1 << CLS_COOK)) shade_body<CLS_COOK, false>(S, rc, pb, b, 0, sm_stack);
         grid.sync();
         if (rc.sample_lights) {
             shadow_body<COUNT, WIDE>(S, rc, pb, b, 0, cnt, sm_stack);

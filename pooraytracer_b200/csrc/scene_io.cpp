@@ -20,9 +20,10 @@
  *     quads are split along the shorter diagonal, larger polygons as a fan;
  *   - materials: tinyobjloader's defaults (Kd = Ks = 0, Ns = 1), map_Kd / map_Ks with options
  *     skipped; tinyxml2's QueryDoubleAttribute / QueryIntAttribute are sscanf("%lf") / ("%d").
- * PNG / BMP / PNM decoding is lossless, so any correct decoder returns stb_image's bytes; JPEG is
- * not decoded (stb's IDCT and chroma upsampling cannot be restated bit for bit without its
- * source): such a texture is reported in prt_model_warnings and behaves like the reference's failed
+ * PNG / BMP / PNM decoding is lossless, so any correct decoder returns stb_image's bytes; JPEG is not, and
+ * jpeg_decode.cpp restates stb_image's integer IDCT, chroma upsampling and colour conversion so that a .jpg map gives
+ * the reference's texels (pinned against the stb_image.h the reference vendors). A texture that cannot be decoded
+ * (CMYK / arithmetic-coded JPEG, other formats) is reported in prt_model_warnings and behaves like the reference's failed
  * load (cyan, Source/Texture.cpp:24).
  */
 #include <algorithm>
@@ -38,6 +39,8 @@
 #include <string>
 #include <unordered_map>
 #include <unordered_set>
+
+#include "jpeg_decode.h"
 #include <vector>
 
 #include "../../include/prt_b200.h"
@@ -66,6 +69,16 @@ bool read_file(const std::string& path, std::vector<uint8_t>& out) {
 /* ------------------------------------------------------------------------------------------------
  * tinyobjloader's tryParseDouble, restated (see the header comment). Returns false when [s, e) does
  * not start a number; tinyobjloader then keeps the caller's default (0.0).
+ *
+ * ATTRIBUTION: this one function follows tinyobjloader's digit-accumulating parser step for step (same state
+ * machine, same order of floating-point operations), because the reference's vertex coordinates are the bits
+ * THAT parser produces — strtod rounds correctly and differs in the last place on about one literal in ten.
+ * tinyobjloader is Copyright (c) 2012-Present Syoyo Fujita and many contributors, released under the MIT License
+ * (https://github.com/tinyobjloader/tinyobjloader, LICENSE: "Permission is hereby granted, free of charge, to any
+ * person obtaining a copy of this software and associated documentation files (the "Software"), to deal in the
+ * Software without restriction ... THE SOFTWARE IS PROVIDED "AS IS", WITHOUT WARRANTY OF ANY KIND ..."). The
+ * reference pins it as an un-vendored submodule (absent from /root/reference), so its behaviour here is restated
+ * from the published algorithm and cannot be pinned against the reference tree.
  * ---------------------------------------------------------------------------------------------- */
 inline bool is_digit(char c) { return c >= '0' && c <= '9'; }
 
@@ -524,7 +537,11 @@ bool load_image(const std::string& path, Image& im, std::string& why) {
     if (f.size() >= 8 && f[0] == 137 && f[1] == 'P') return decode_png(f, im, why);
     if (f.size() >= 2 && f[0] == 'B' && f[1] == 'M') return decode_bmp(f, im, why);
     if (f.size() >= 2 && f[0] == 'P' && (f[1] == '5' || f[1] == '6')) return decode_pnm(f, im, why);
-    if (f.size() >= 3 && f[0] == 0xff && f[1] == 0xd8) { why = "JPEG decoding is not implemented (" + path + ")"; return false; }
+    if (f.size() >= 3 && f[0] == 0xff && f[1] == 0xd8) {
+        if (prt::decode_jpeg(f.data(), f.size(), im.w, im.h, im.c, im.px, why)) return true;
+        why += " (" + path + ")";
+        return false;
+    }
     why = "unknown image format (" + path + ")";
     return false;
 }

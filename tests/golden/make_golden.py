@@ -105,8 +105,34 @@ def output_stage_fixture():
     print("output_stage", img.shape, "steps", steps.view(np.float64)[[0, 1, 127, 253]], "bytes used", len(np.unique(rgb8)))
 
 
+def jpeg_fixture():
+    """f1: 60 of the JPEG files of tests/test_scene_io.py:jpeg_cases() (written by PIL here) with the texels the stb_image.h
+    vendored by the reference decodes them to (stbi_load inside oracle/_ref/libprt_ref.so, compiled from the reference's
+    own Texture.cpp). The fixture pins pooraytracer_b200/csrc/jpeg_decode.cpp on boxes without oracle/_ref."""
+    import io
+    import tempfile
+    from PIL import Image
+    import test_scene_io as tsi
+    out = {}
+    all_cases = tsi.jpeg_cases()
+    pick = all_cases[::max(1, len(all_cases) // 60)][:60]
+    with tempfile.TemporaryDirectory(prefix="prt_jpg_") as d:
+        for name, kw, img in pick:
+            p = os.path.join(d, "t.jpg")
+            try:
+                Image.fromarray(img).save(p, "JPEG", **kw)
+            except Exception:
+                continue
+            out["file_" + name] = np.frombuffer(open(p, "rb").read(), np.uint8)
+            out["stb_" + name] = tsi._stb_load(p)
+    np.savez_compressed(os.path.join(HERE, "jpeg_fixture.npz"), **out)
+    print("jpeg_fixture", len(out) // 2, "files", sum(v.nbytes for k, v in out.items() if k.startswith("file_")), "bytes of JPEG")
+
+
 def main():
     assert ol.available("ref"), "build oracle/_ref first (make -C oracle ref)"
+    if len(sys.argv) > 1 and sys.argv[1] == "jpeg":
+        return jpeg_fixture()
     if len(sys.argv) > 1 and sys.argv[1] == "output":
         return output_stage_fixture()
     if len(sys.argv) > 1 and sys.argv[1] == "cook":
@@ -166,6 +192,7 @@ def main():
             render_fixture(name)
     cook_fixtures()
     output_stage_fixture()
+    jpeg_fixture()
 
 
 if __name__ == "__main__":

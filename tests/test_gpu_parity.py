@@ -153,6 +153,42 @@ def test_stack_overflow_falls_back_to_the_reference_walk():
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-2000:]
 
 
+def test_reference_walk_overflow_is_reported(gpu_ctx):
+    """The reference-order walk (trace_reference, traverse.cuh) has its own stack; its depth is log2(mesh size) + the top
+    level, so the shipped 64 entries never fill — but if they did, a subtree would be LOST, so the walk counts every drop
+    in a sticky counter that prt_get_stats surfaces. Healthy build: 0 after a full render and a ray batch. A build with a
+    3-entry stack (made by __graft_entry__.build()): > 0 on the same work."""
+    import subprocess, sys, textwrap
+    sc = cases.cornell_small()
+    o, d = cases.ray_batch(sc)
+    s = Scene(gpu_ctx, sc, accel=capi.ACCEL_REFERENCE_BVH2)
+    s.trace_closest(o, d)
+    s.render(make_camera(sc.camera, 32, 32), make_params(2, 6, rng_key=3))
+    assert s.stats().ref_stack_overflows == 0
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(root, "pooraytracer_b200", "libprt_b200_refstack3.so")
+    if not os.path.exists(lib):
+        pytest.skip("libprt_b200_refstack3.so not built")
+    code = textwrap.dedent("""
+        import os, sys
+        import numpy as np
+        sys.path.insert(0, os.path.join(%r, "tests")); sys.path.insert(0, %r)
+        import cases
+        from pooraytracer_b200 import Context, Scene, _capi as capi
+        sc = cases.cornell_small()
+        o, d = cases.ray_batch(sc)
+        s = Scene(Context(0), sc, accel=capi.ACCEL_REFERENCE_BVH2)
+        s.trace_closest(o, d)
+        n = s.stats().ref_stack_overflows
+        assert n > 0, n
+        s.trace_closest(o[:1], d[:1])
+        assert s.stats().ref_stack_overflows >= n   # sticky
+        print("ok", n)
+    """ % (root, root))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, PRT_B200_LIB=lib), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-2000:]
+
+
 def test_counters_and_stats(gpu_ctx):
     sc = cases.cornell_small()
     o, d = cases.ray_batch(sc)

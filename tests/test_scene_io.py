@@ -15,6 +15,8 @@ import numpy as np
 import pytest
 
 import cases
+import oracle_lib as ol
+from pooraytracer_b200 import api
 from pooraytracer_b200 import Context, Model, PrtError, Scene, _capi as capi, load_image, make_camera, make_params, scenes, write_hdr, write_png
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -199,6 +201,101 @@ def test_png_decoder(built, tmp_path):
         load_image(str(tmp_path / "x.jpg"))
 
 
+def jpeg_cases():
+    """(name, PIL save options, picture) of the JPEG fixture set: baseline / progressive, every chroma layout PIL writes,
+    grey, restart intervals, sizes that are not multiples of the MCU, smooth / noisy / hard-edged content"""
+    import itertools
+    rng = np.random.default_rng(5)
+    out = []
+    for (w, h), kind, sub, prog, q, grey, rst in itertools.product([(1, 1), (7, 5), (17, 33), (64, 48), (129, 64)], ["smooth", "noise", "checker"],
+                                                                   [0, 1, 2, "4:4:0", "4:1:1"], [False, True], [35, 100], [False, True], [0, 3]):
+        if grey and sub != 0:
+            continue
+        y, x = np.mgrid[0:h, 0:w]
+        if kind == "smooth":
+            img = np.stack([128 + 100 * np.sin(x / 7.0) * np.cos(y / 11.0), 128 + 90 * np.cos(x / 5.0 + y / 9.0), 30 + (x * 3 + y * 5) % 200], -1)
+        elif kind == "noise":
+            img = rng.integers(0, 256, (h, w, 3))
+        else:
+            img = ((x // 4 + y // 4) % 2 * 255)[..., None].repeat(3, -1) * np.array([1, 0.5, 0.2])
+        img = np.clip(img, 0, 255).astype(np.uint8)
+        kw = dict(quality=q, progressive=prog)
+        if not grey:
+            kw["subsampling"] = sub
+        if rst:
+            kw["restart_marker_blocks"] = rst
+        out.append((f"{w}x{h}_{kind}_{str(sub).replace(':', '')}_{int(prog)}_{q}_{int(grey)}_{rst}", kw, img[..., 0] if grey else img))
+    return out
+
+
+def _stb_load(path):
+    """stbi_load(path, &w, &h, &c, 0) of the stb_image.h the reference vendors, as compiled into oracle/_ref by the
+    reference's own Texture.cpp (test infrastructure)"""
+    import ctypes as C
+    lib = ol.OracleLib("ref").lib
+    lib.stbi_load.restype = C.POINTER(C.c_ubyte)
+    lib.stbi_load.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int]
+    w, h, c = C.c_int(), C.c_int(), C.c_int()
+    ptr = lib.stbi_load(path.encode(), C.byref(w), C.byref(h), C.byref(c), 0)
+    assert ptr, path
+    a = np.ctypeslib.as_array(ptr, shape=(h.value, w.value, c.value)).copy()
+    lib.stbi_image_free(ptr)
+    return a
+
+
+def test_jpeg_decoder_matches_stb_image(built, tmp_path):
+    """f1: ImageTexture loads whatever stbi_load reads (Source/Texture.cpp:10-21), and a JPEG decoder's
+    output is an implementation choice (IDCT, chroma upsampling, colour conversion): jpeg_decode.cpp must return stb's
+    bytes. Live against the vendored stb_image where oracle/_ref is present (every file of jpeg_cases(), ~500), and
+    always against the committed fixture (tests/golden/jpeg_fixture.npz: 60 files with the bytes stb decoded)."""
+    from PIL import Image
+    g = np.load(os.path.join(ROOT, "tests", "golden", "jpeg_fixture.npz"))
+    names = [n[5:] for n in g.files if n.startswith("file_")]
+    assert len(names) >= 40
+    for n in names:
+        p = str(tmp_path / "f.jpg")
+        open(p, "wb").write(g["file_" + n].tobytes())
+        got = load_image(p)
+        want = g["stb_" + n]
+        assert np.array_equal(got.reshape(want.shape), want), n
+    if not ol.available("ref"):
+        return
+    checked = 0
+    for name, kw, img in jpeg_cases():
+        p = str(tmp_path / "t.jpg")
+        try:
+            Image.fromarray(img).save(p, "JPEG", **kw)
+        except Exception:
+            continue  # an option this PIL build does not know
+        want = _stb_load(p)
+        got = load_image(p)
+        assert got.size == want.size and np.array_equal(got.reshape(want.shape), want), name
+        checked += 1
+    assert checked > 300
+
+
+def test_jpeg_texture_in_a_scene(built, tmp_path):
+    """a map_Kd that names a .jpg is loaded (round 1 reported it and rendered cyan): the model's texture holds stb's texels"""
+    from PIL import Image
+    sc = cases.bathroom_small()
+    d = _write(tmp_path, sc)
+    mtl = [f for f in os.listdir(d) if f.endswith(".mtl")][0]
+    text = open(os.path.join(d, mtl)).read()
+    pngs = [f for f in os.listdir(d) if f.endswith(".png")]
+    first = sorted(pngs)[0]
+    rgb = Image.open(os.path.join(d, first)).convert("RGB")
+    rgb.save(os.path.join(d, "wall.jpg"), "JPEG", quality=92, subsampling=2)
+    assert first in text
+    open(os.path.join(d, mtl), "w").write(text.replace(first, "wall.jpg"))
+    m = Model(d, "s")
+    assert not any("wall.jpg" in w for w in m.warnings)
+    tex = [t for t in (m.texture(i) for i in range(m.desc.n_textures)) if t is not None and t.shape[2] == 3]
+    want = load_image(os.path.join(d, "wall.jpg"))
+    assert any(t.shape == want.shape and np.array_equal(t, want) for t in tex)
+    if ol.available("ref"):
+        assert np.array_equal(want, _stb_load(os.path.join(d, "wall.jpg")))
+
+
 def test_image_writers(built, tmp_path):
     rng = np.random.default_rng(7)
     img = rng.integers(0, 256, size=(70, 333, 3), dtype=np.uint8)  # > 65535 bytes: several stored blocks
@@ -277,10 +374,12 @@ def test_prt_main_drop_in(gpu_ctx, tmp_path):
     png = load_image(out + ".png")
     s = Scene(gpu_ctx, sc)
     cam = make_camera(sc.camera)
-    parts = [s.render(cam, make_params(6, 8, rng_key=4, spp_begin=b, spp_end=e)) for b, e in ((0, 4), (4, 6))]
-    img = parts[0] + parts[1]
-    import torch
-    rgb8, f32 = s.resolve_device(torch.from_numpy(img).cuda().data_ptr(), cam.image_width, cam.image_height)
+    img = s.render(cam, make_params(6, 8, rng_key=4))  # prt_main renders through prt_multi_render: one call, passes cut by the library
+    rgb8, f32 = s.resolve(img)
     assert np.array_equal(png, rgb8)
     hdr = open(out + ".hdr", "rb").read()
     assert hdr.startswith(b"#?RADIANCE") and len(hdr) > cam.image_width * cam.image_height * 4
+    import imgutil
+    api.write_hdr(out + "_check.hdr", f32)
+    assert np.array_equal(imgutil.hdr_rgbe(hdr), imgutil.hdr_rgbe(open(out + "_check.hdr", "rb").read()))
+    assert "job: load" in r.stdout and "1 GPU" in r.stdout

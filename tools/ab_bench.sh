@@ -7,7 +7,7 @@ RQ=0; if [ "$1" = "rq" ]; then RQ=1; shift; fi
 for n in "$@"; do
   lib=$PWD/pooraytracer_b200/csrc/build/variants/lib_$n.so
   [ -f "$lib" ] || { echo "missing $lib"; continue; }
-  PRT_B200_LIB=$lib timeout 300 python bench.py --no-cpu-baseline --steps 4 --warmup 3 > gpurun_out/ab_$n.json 2> gpurun_out/ab_$n.err
+  PRT_B200_LIB=$lib timeout 300 python bench.py --no-cpu-baseline --headline-only --steps 4 --warmup 3 > gpurun_out/ab_$n.json 2> gpurun_out/ab_$n.err
   python - "$n" <<'PY'
 import json,sys
 n=sys.argv[1]
@@ -18,7 +18,7 @@ except Exception as e:
     print(n,'FAILED',e)
 PY
   if [ -n "$AB_BATH" ]; then
-    PRT_B200_LIB=$lib timeout 300 python bench.py --scene bathroom2 --width 1280 --height 720 --depth 50 --steps ${AB_BATH_STEPS:-2} --no-cpu-baseline > gpurun_out/ab_bath_$n.json 2> gpurun_out/ab_bath_$n.err
+    PRT_B200_LIB=$lib timeout 300 python bench.py --scene bathroom2 --width 1280 --height 720 --depth 50 --steps ${AB_BATH_STEPS:-2} --no-cpu-baseline --headline-only > gpurun_out/ab_bath_$n.json 2> gpurun_out/ab_bath_$n.err
     python - "$n" <<'PY'
 import json,sys
 n=sys.argv[1]
