@@ -19,8 +19,8 @@
  *   An Adobe APP14 segment with transform 0, or component ids 'R','G','B' without a JFIF header, means the three
  *   planes are RGB already; one component decodes to one channel (stbi_load with req_comp = 0).
  *
- * Pinned against the stb_image.h the reference vendors — compiled into oracle/_ref/libprt_ref.so as part of the
- * reference's own Texture.cpp — on baseline / progressive / 4:4:4 / 4:2:2 / 4:2:0 / 4:4:0 / 4:1:1 / grey files with odd
+ * Pinned by the test suite against the stb_image.h the reference vendors (compiled, as part of the reference's own
+ * Texture.cpp, into the reference checker the tests load; this library never does) on baseline / progressive / 4:4:4 / 4:2:2 / 4:2:0 / 4:4:0 / 4:1:1 / grey files with odd
  * sizes and restart intervals (tests/test_scene_io.py, tests/golden/jpeg_*.npz). Four-component (CMYK / YCCK) and
  * arithmetic-coded files are refused, as are 12-bit ones (stb refuses those too).
  */
