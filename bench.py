@@ -637,7 +637,7 @@ def run_b200(a):
             v, info = cpu_reference_leg(a.scene, a.width, a.height, a.depth, a.total_spp, a.cpu_spp or 12)
             line["cpu_baseline"] = {"value": v, "unit": "spp/s", "cores": info["cores"], "kind": info["kind"], "sample": info["sample"],
                                     "mrays_s": info["mrays_s"]}
-            vs, infos = cpu_reference_leg(a.scene, a.width, a.height, a.depth, a.total_spp, 2, variant="shipped")
+            vs, infos = cpu_reference_leg(a.scene, a.width, a.height, a.depth, a.total_spp, 1, variant="shipped")  # ~30 s of 16 cores: glibc rand() serialises the threads
             if vs is not None:
                 line["cpu_baseline"]["as_shipped"] = {"value": vs, "unit": "spp/s", "cores": infos["cores"], "sample": infos["sample"], "mrays_s": infos["mrays_s"]}
         print(json.dumps(line), flush=True)

@@ -23,9 +23,9 @@
                                     /* hit triangle can be recovered from HitRecord::material      */
 #define ORC_UV_TAG 2                /* texcoords := (0,0),(1,0),(0,1): HitRecord::uv == (alpha,beta) */
 #define ORC_DEFINE_UB 4             /* Phong: caller's `attenuation` pre-set to 0 before Scatter   */
-                                    /* (Camera.cpp:177 leaves it uninitialised). Nothing else: the */
-                                    /* draw inside Eval (Material.h:228) advances the stream as in */
-                                    /* the unmodified reference                                    */
+                                    /* (Camera.cpp:177 leaves it uninitialised), and the stream is */
+                                    /* rewound after the draw inside Eval (Material.h:228): not UB, */
+                                    /* but visibility-dependent (see PhongDefined, ref_driver.cpp)  */
 
 /* rng modes for render */
 #define ORC_RNG_COUNTER 0      /* rng_spec.h, keyed by (rng_key, pixel, sample, dim) — parity       */

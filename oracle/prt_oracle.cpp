@@ -20,6 +20,9 @@
  * Two reference spots are undefined behaviour; like ORC_DEFINE_UB in ref_driver.cpp the port
  * defines them: Phong's unset `attenuation` (Camera.cpp:177, Material.h:280-284) is 0, and a
  * shadow ray that hits nothing (Camera.cpp:150-152 reads an unset position) is "not visible".
+ * A third spot is defined behaviour that a wavefront cannot follow: the draw inside
+ * PhoneReflectance::Eval (Material.h:228) advances the stream only if the light sample was visible;
+ * the port rewinds it (see PhongDefined in ref_driver.cpp for the full argument).
  */
 #include <algorithm>
 #include <atomic>
@@ -568,8 +571,11 @@ V3 mat_eval(const Scene& s, const Mat& m, V3 wi, const EvalCtx& c, Rng& rng) {
     switch (m.type) {
         case PRT_MAT_LAMBERTIAN:  // Material.h:128-130
             return tex_or_color(s, m.kd_tex, m.kd, c.uv) * InvPi;
-        case PRT_MAT_PHONG: {  // Material.h:227-248: draws a number (Material.h:228) — an ordinary, stream-advancing draw
+        case PRT_MAT_PHONG: {  // Material.h:227-248: draws a number (Material.h:228); the stream is REWOUND after it, as in
+                               // ref_driver.cpp's PhongDefined (the advance would depend on the shadow ray's outcome)
+            uint32_t saved = rng.dim;
             double u = rng.RandomDouble();
+            if (rng.mode == ORC_RNG_COUNTER && !rng.script) rng.dim = saved;
             if (u < m.pkd) {
                 if (wi.z <= 0) return v3(0, 0, 0);
                 return tex_or_color(s, m.kd_tex, m.kd, c.uv) * InvPi;

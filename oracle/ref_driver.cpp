@@ -158,9 +158,18 @@ private:
     const Hittable& inner;
 };
 
-// ORC_DEFINE_UB: gives the ONE undefined spot of the Phong material a defined meaning while the reference's own
-// Scatter body still does all the work. (PhoneReflectance::Eval's RandomDouble(), Material.h:228, is NOT undefined: it
-// is an ordinary draw that advances the stream, and it does so here exactly as in the unmodified reference.)
+// ORC_DEFINE_UB: two spots of the Phong material get a defined meaning while the reference's own Scatter / Eval
+// bodies still do all the work.
+//  (1) Scatter's `attenuation` is left uninitialised when pdf == 0 (Camera.cpp:177, Material.h:280-284): genuinely
+//      undefined behaviour; pre-set to 0.
+//  (2) PhoneReflectance::Eval draws a random number (Material.h:228). That is NOT undefined behaviour — it is an
+//      ordinary rand() call that advances the stream — but Camera::RayColor only reaches Eval when the light sample
+//      turned out VISIBLE (Camera.cpp:152-155), so whether the Russian-roulette and scatter draws that follow are
+//      shifted by one depends on the outcome of the shadow ray. A wavefront integrator scatters BEFORE it traces its
+//      shadow rays and cannot reproduce a visibility-dependent stream position; the draw's VALUE never matters where
+//      Eval is reachable (Ns <= 1 => pkd = 1 => u < pkd always), so the estimator is unchanged if the stream is rewound
+//      after it. Phong render parity (tests/golden/render_*: vertices with Ns <= 1) is therefore against this REWOUND
+//      stream, not against the unmodified reference's stream; every other material consumes the unmodified stream.
 class PhongDefined : public PhoneReflectance {
 public:
     using PhoneReflectance::PhoneReflectance;
@@ -168,6 +177,13 @@ public:
                  Ray& scatteredRay) const override {
         attenuation = color(0., 0., 0.);  // Camera.cpp:177 leaves it uninitialised
         return PhoneReflectance::Scatter(rayIn, record, attenuation, scatteredRay);
+    }
+    vec3 Eval(const vec3& wi, const MaterialEvalContext& context) const override {
+        ThreadState& t = tls();
+        uint32_t saved = t.dim;
+        vec3 f = PhoneReflectance::Eval(wi, context);
+        if (t.mode == MODE_COUNTER) t.dim = saved;  // Material.h:228 draw: value never matters, position rewound (see above)
+        return f;
     }
 };
 

@@ -649,7 +649,7 @@ __device__ __forceinline__ void shade_vertex(const DevScene& S, const RenderCons
 #define PRT_SHADE_STAGE 1 /* 1: persistent warps over contiguous chunks, pushes staged in shared memory; 0: round 1's grid-stride loop */
 #endif
 #ifndef PRT_SHADE_CHUNK_ITERS
-#define PRT_SHADE_CHUNK_ITERS 8
+#define PRT_SHADE_CHUNK_ITERS 4 /* measured 2 / 4 / 8 / 16: k_shade 20.2 / 20.4 / 20.9 / 21.3 ms (profiles/r2_s5_chunk_ab.txt) */
 #endif
 #ifndef PRT_SHADE_AHEAD
 #define PRT_SHADE_AHEAD 0 /* 1: read the next vertex's primitive id an iteration ahead and prefetch its TriShade line into L1.

@@ -14,9 +14,12 @@
  *                                                                Material.h:106-151,183-226,262-312,334-363
  *
  * Defined meaning of the reference's undefined spot: Phong's unset `attenuation`
- * (Camera.cpp:177, Material.h:280-284) is 0. The random number drawn inside PhoneReflectance::Eval
- * (Material.h:228) is an ordinary draw: its value never matters where Eval is reachable (Ns <= 1 => pkd = 1), but it
- * advances the stream, here as in the unmodified reference.
+ * (Camera.cpp:177, Material.h:280-284) is 0. The random number drawn inside PhoneReflectance::Eval (Material.h:228)
+ * is NOT undefined — it is an ordinary draw — but the reference reaches Eval only when the light sample was VISIBLE
+ * (Camera.cpp:152-155), so the position of every later draw of the path would depend on the shadow ray's outcome,
+ * which a wavefront learns only after it has scattered. Its value never matters where Eval is reachable (Ns <= 1 =>
+ * pkd = 1), so here — and in both CPU checkers, identically — the draw is peeked and the stream is not advanced:
+ * the estimator is the reference's, the stream of Phong paths is shifted by one against the unmodified reference.
  */
 #ifndef PRT_SHADING_CUH
 #define PRT_SHADING_CUH
@@ -153,11 +156,11 @@ __device__ __forceinline__ d3 reflect(d3 wo, d3 n) { return -wo + 2. * dot(wo, n
 /* ---- BSDFs ------------------------------------------------------------------------------------- */
 /* Material::Eval as the NEE estimator calls it (Camera.cpp:168); wi, wo in the local frame */
 __device__ __forceinline__ d3 cook_eval(const DevMaterial& m, d3 wi, d3 wo); /* cook_torrance.cuh */
-__device__ __forceinline__ d3 material_eval(const DevScene& S, const DevMaterial& m, d3 wi, d3 wo, d2 uv, Rng& rng) {
+__device__ __forceinline__ d3 material_eval(const DevScene& S, const DevMaterial& m, d3 wi, d3 wo, d2 uv, const Rng& rng) {
     if (m.type == PRT_MAT_COOK_TORRANCE) return cook_eval(m, wi, wo);
     if (m.type == PRT_MAT_LAMBERTIAN) return tex_or_color(S, m.kd_tex, m.kd, uv) * PRT_INV_PI;
     if (m.type == PRT_MAT_PHONG) {
-        const double u = rng.next(); /* PhoneReflectance::Eval draws a number (Material.h:228): it advances the stream like any other draw */
+        const double u = rng.peek(); /* Material.h:228: the value is looked at, the stream position is not moved (header comment) */
         if (u < m.pkd) {
             if (wi.z <= 0) return mk3(0, 0, 0);
             return tex_or_color(S, m.kd_tex, m.kd, uv) * PRT_INV_PI;
