@@ -494,6 +494,10 @@ def run_b200(a):
         import datetime
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(minutes=40))
+        # the ranks that only wait (while rank 0 drives every GPU through the C ABI's whole-box handle) must wait on the HOST:
+        # an NCCL barrier is a kernel spinning on their GPU, and rank 0's kernels on that GPU — another process, another
+        # CUDA context — would be time-sliced against it
+        host_group = dist.new_group(backend="gloo", timeout=datetime.timedelta(minutes=40))
     accel = getattr(capi, ACCELS[a.accel])
     sc = make_scene(a.scene)
     ctx = Context(local)
@@ -598,6 +602,7 @@ def run_b200(a):
     del acc
     torch.cuda.empty_cache()
     barrier()
+    torch.cuda.synchronize()
     if rank == 0:
         devices = list(range(world))
         box = MultiScene(devices, sc, accel=accel, max_leaf=a.max_leaf)
@@ -642,7 +647,7 @@ def run_b200(a):
                 line["cpu_baseline"]["as_shipped"] = {"value": vs, "unit": "spp/s", "cores": infos["cores"], "sample": infos["sample"], "mrays_s": infos["mrays_s"]}
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=host_group)
         dist.destroy_process_group()
 
 

@@ -3,13 +3,13 @@
 # launches per 64-spp cornell step: k_primary 1, k_extend 24 (bounces 1..24), k_shade 25, k_shadow 25, k_tail 1 (bounces 25..100);
 # bench.py runs an instrumented step first (the COUNT instantiations match the same regex), so skip one step's worth.
 TAG=${TAG:-r2}
-B="python bench.py --steps 1 --warmup 1 --no-cpu-baseline"
+B="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --headline-only"
 N="ncu --set full --clock-control none --import-source on"
 $N -k regex:k_extend -s 24 -c 2 -o gpurun_out/${TAG}_extend -f $B > gpurun_out/${TAG}_ncu1.log 2>&1; echo "extend rc=$?"
 $N -k regex:k_shade -s 25 -c 2 -o gpurun_out/${TAG}_shade -f $B > gpurun_out/${TAG}_ncu2.log 2>&1; echo "shade rc=$?"
 $N -k regex:k_shadow -s 25 -c 2 -o gpurun_out/${TAG}_shadow -f $B > gpurun_out/${TAG}_ncu3.log 2>&1; echo "shadow rc=$?"
 if [ -z "$NCU_SKIP_BATH" ]; then
-$N -k regex:k_extend -s 13 -c 2 -o gpurun_out/${TAG}_bath_extend -f python bench.py --scene bathroom2 --width 1280 --height 720 --depth 50 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/${TAG}_ncu4.log 2>&1; echo "bath rc=$?"
+$N -k regex:k_extend -s 13 -c 2 -o gpurun_out/${TAG}_bath_extend -f python bench.py --scene bathroom2 --steps 1 --warmup 1 --no-cpu-baseline --headline-only > gpurun_out/${TAG}_ncu4.log 2>&1; echo "bath rc=$?"
 $N -k regex:k_trace_closest -s 1 -c 2 -o gpurun_out/${TAG}_rq10 -f python tools/rayquery_bench.py --tris 10 --rays 24 --reps 1 > gpurun_out/${TAG}_ncu5.log 2>&1; echo "rq rc=$?"
 fi
 # condense on the box: the reports themselves exceed what gpurun copies back (64 MiB)

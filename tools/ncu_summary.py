@@ -10,7 +10,8 @@ import sys
 KEEP = re.compile(
     r"^(gpu__time_duration\.sum|dram__bytes_(read|write)\.sum(\.per_second)?|gpu__dram_throughput\.avg\.pct|"
     r"lts__t_sector_hit_rate\.pct|lts__t_bytes\.sum(\.per_second)?|lts__throughput\.avg\.pct|l1tex__t_sector_hit_rate\.pct|"
-    r"l1tex__throughput\.avg\.pct_of_peak_sustained_active|l1tex__t_bytes\.sum|"
+    r"l1tex__throughput\.avg\.pct_of_peak_sustained_active|l1tex__t_bytes\.sum|l1tex__[a-z0-9_]+\.(avg|sum)(\.pct_of_peak_sustained_(active|elapsed))?$|"
+    r"lts__[a-z0-9_]+\.(avg|sum)\.pct_of_peak_sustained_elapsed$|smsp__inst_executed_op_(shared|global|local)_(ld|st)\.sum|"
     r"launch__(grid_size|block_size|registers_per_thread|occupancy_limit_registers)|"
     r"sm__warps_active\.avg\.pct|sm__throughput\.avg\.pct|smsp__issue_active\.avg\.pct|"
     r"smsp__inst_executed\.sum|smsp__thread_inst_executed_per_inst_executed\.ratio|"
