@@ -215,6 +215,10 @@ int prt_scene_create(prt_context* ctx, const prt_scene_desc* desc, prt_scene** o
 /* Flattens into the chosen layout and uploads to HBM. */
 int prt_scene_commit(prt_scene* scene, const prt_build_opts* opts);
 void prt_scene_destroy(prt_scene* scene);
+/* A replica of a COMMITTED scene on another context's GPU: the device buffers are copied GPU to GPU (NVLink between peers),
+ * nothing is rebuilt on the host. This is how prt_multi_create replicates the scene over the box. The replica renders and
+ * answers ray queries like the original; prt_scene_reference_order answers on the original only. */
+int prt_scene_clone(const prt_scene* source, prt_context* ctx, prt_scene** out);
 
 /* Host-side introspection (no GPU needed): the reference DFS order the tie rule relies on.
  * world_rank[prim] = position of the triangle in the left-to-right leaf order of the reference
@@ -277,8 +281,8 @@ int prt_resolve(prt_scene* scene, const double* rgb, int32_t width, int32_t heig
 int prt_resolve_thresholds(double* out254);
 
 /* ---- the whole box: 1..8 GPUs behind one handle ------------------------------
- * Replaces main.cpp:36-52 for a caller that wants every GPU of the node: the scene is replicated (copied, flattened
- * and uploaded once per GPU, concurrently), Camera::Render's samples are split into contiguous ranges across the GPUs
+ * Replaces main.cpp:36-52 for a caller that wants every GPU of the node: the scene is replicated (ingested, built and
+ * uploaded ONCE, on devices[0], then copied GPU to GPU: prt_scene_clone), Camera::Render's samples are split into contiguous ranges across the GPUs
  * (the generator is keyed by the absolute sample index, so the union of the shards is the one-GPU image up to the order
  * of the final FP64 additions), and ONE collective — ncclReduce(sum, double, W*H*3) to devices[0] over NVLink — ends
  * the render. The library owns the communicator; NCCL is bound at run time and only when n > 1. Used from one host

@@ -142,6 +142,7 @@ PROTOTYPES = {
     "prt_scene_create": (C.c_int, [C.c_void_p, C.POINTER(PrtSceneDesc), C.POINTER(C.c_void_p)]),
     "prt_scene_commit": (C.c_int, [C.c_void_p, C.POINTER(PrtBuildOpts)]),
     "prt_scene_destroy": (None, [C.c_void_p]),
+    "prt_scene_clone": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
     "prt_scene_reference_order": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
     "prt_trace_closest": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 8),
     "prt_trace_any": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 5),

@@ -244,6 +244,14 @@ class Scene:
         if accel is not None:
             self.commit(accel)
 
+    def clone(self, ctx: "Context") -> "Scene":
+        """prt_scene_clone: a replica of this committed scene on ctx's GPU (device-to-device copies, no host rebuild)"""
+        h = C.c_void_p()
+        _check(self.lib, self.lib.prt_scene_clone(self.handle, ctx.handle, C.byref(h)))
+        other = Scene.__new__(Scene)
+        other.ctx, other.lib, other.data, other.handle = ctx, self.lib, self.data, h
+        return other
+
     def commit(self, accel: int, max_leaf: int = 0):
         """prt_scene_commit; max_leaf = triangles per leaf of the SAH / LBVH trees (0: the default, 4)"""
         o = capi.PrtBuildOpts()

@@ -281,6 +281,8 @@ void camera_setup(const prt_camera* c, RenderConst& rc) {
     const d3 vu = vw * u;
     const d3 vv = vh * (-v);
     rc.width = W; rc.height = H; rc.npix = W * H;
+    rc.by_width = FastDiv::make((uint32_t)W);
+    rc.by_npix = FastDiv::make((uint32_t)(W * H));
     rc.center = eye;
     rc.dU = vu / (double)W;
     rc.dV = vv / (double)H;
@@ -513,6 +515,83 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
         CUDA_TRY(cudaEventCreate(&s->ev1));
     }
     s->committed = true;
+    return PRT_OK;
+}
+
+/* A replica of a committed scene on another GPU: every device buffer is copied GPU to GPU (cudaMemcpyPeer: NVLink when the
+ * devices are peers), the pointer table is rebound, nothing is rebuilt or re-uploaded from the host. The replica holds no
+ * host-side scene (prt_scene_reference_order answers on the original only). */
+int prt_scene_clone(const prt_scene* src, prt_context* ctx, prt_scene** out) {
+    if (!src || !ctx || !out) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_scene_clone: null argument");
+    *out = nullptr;
+    if (!src->committed || !src->ctx || src->ctx->device < 0 || ctx->device < 0)
+        return fail(PRT_ERR_NO_DEVICE, "prt_scene_clone: source and destination must be committed, GPU-bound scenes / contexts");
+    prt_scene* s = new (std::nothrow) prt_scene();
+    if (!s) return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_clone: out of host memory");
+    s->ctx = ctx;
+    s->accel = src->accel;
+    s->has_cook = src->has_cook;
+    s->class_mask = src->class_mask;
+    s->device_build_ms = src->device_build_ms;
+    s->stats = src->stats;
+    for (int k = 0; k < 3; ++k) { s->key_lo[k] = src->key_lo[k]; s->key_scale[k] = src->key_scale[k]; }
+    const int sd = src->ctx->device, dd = ctx->device;
+    cudaStream_t st = ctx->stream;
+    auto bail = [&](cudaError_t e, const char* what) {
+        const std::string msg = std::string("prt_scene_clone: ") + what + ": " + cudaGetErrorString(e);
+        delete s;
+        return fail(e == cudaErrorMemoryAllocation ? PRT_ERR_OUT_OF_MEMORY : PRT_ERR_CUDA, msg);
+    };
+    cudaError_t e = cudaSetDevice(dd);
+    if (e != cudaSuccess) return bail(e, "cudaSetDevice");
+    /* make sure the source's uploads have landed before they are read from another device's stream */
+    cudaSetDevice(sd);
+    e = cudaStreamSynchronize(src->ctx->stream);
+    cudaSetDevice(dd);
+    if (e != cudaSuccess) return bail(e, "cudaStreamSynchronize(source)");
+#define PRT_CLONE(member)                                                                                                        \
+    do {                                                                                                                         \
+        if (src->member.p && src->member.n) {                                                                                    \
+            e = s->member.ensure(src->member.n);                                                                                 \
+            if (e != cudaSuccess) return bail(e, "allocate " #member);                                                           \
+            e = cudaMemcpyPeerAsync(s->member.p, dd, src->member.p, sd, src->member.n * sizeof(*src->member.p), st);             \
+            if (e != cudaSuccess) return bail(e, "copy " #member);                                                               \
+        }                                                                                                                        \
+    } while (0)
+    PRT_CLONE(d_tris); PRT_CLONE(d_slot_prim); PRT_CLONE(d_shade); PRT_CLONE(d_nodes2); PRT_CLONE(d_nodes4); PRT_CLONE(d_nodes4q);
+    PRT_CLONE(d_ref_nodes); PRT_CLONE(d_light_tris); PRT_CLONE(d_light_nodes); PRT_CLONE(d_materials); PRT_CLONE(d_textures);
+    PRT_CLONE(d_texels); PRT_CLONE(d_srgb); PRT_CLONE(d_prim_class);
+#undef PRT_CLONE
+    e = s->d_fetch.ensure(4);
+    if (e == cudaSuccess) e = s->d_counters.ensure(8);
+    if (e == cudaSuccess) e = s->d_err.ensure(1);
+    if (e == cudaSuccess) e = cudaMemsetAsync(s->d_counters.p, 0, 8 * sizeof(unsigned long long), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(s->d_err.p, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return bail(e, "scratch");
+    if (int rc = ensure_sort_scratch(s, st)) { delete s; return rc; }
+    e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+    /* the pointer table: same fields set / unset as in the source, pointing at this GPU's copies */
+    const DevScene& A = src->dev;
+    DevScene& D = s->dev;
+    D = A;
+    D.tris = s->d_tris.p;
+    D.slot_prim = s->d_slot_prim.p;
+    D.shade = s->d_shade.p;
+    D.nodes2 = A.nodes2 ? s->d_nodes2.p : nullptr;
+    D.nodes4 = A.nodes4 ? s->d_nodes4.p : nullptr;
+    D.nodes4q = A.nodes4q ? s->d_nodes4q.p : nullptr;
+    D.ref_nodes = s->d_ref_nodes.p;
+    D.light_tris = s->d_light_tris.p;
+    D.light_nodes = s->d_light_nodes.p;
+    D.materials = s->d_materials.p;
+    D.textures = s->d_textures.p;
+    D.texels = s->d_texels.p;
+    D.srgb_lut = s->d_srgb.p;
+    D.ref_overflow = s->d_err.p;
+    if (cudaEventCreate(&s->ev0) != cudaSuccess || cudaEventCreate(&s->ev1) != cudaSuccess) return bail(cudaErrorUnknown, "cudaEventCreate");
+    s->committed = true;
+    *out = s;
     return PRT_OK;
 }
 

@@ -282,13 +282,14 @@ __device__ __forceinline__ void lum_set(const PathBuffers& pb, int32_t slot, d3 
 
 /* Camera::GetRay (Camera.cpp:108-117): pixel centre, direction not normalised. slot = sample * npix + pixel */
 __device__ __forceinline__ void camera_ray(const RenderConst& rc, int32_t slot, d3& o, d3& d) {
-    const int pix = slot % rc.npix;
-    const int i = pix % rc.width, j = pix / rc.width;
-    double fi = (double)i, fj = (double)j;
+    uint32_t smp, pix, i, j;
+    rc.by_npix.divmod((uint32_t)slot, smp, pix);
+    rc.by_width.divmod(pix, j, i);
+    double fi = (double)(int)i, fj = (double)(int)j;
     if (rc.flags & PRT_RENDER_PIXEL_JITTER) {
         /* the commented-out lines of Camera.cpp:110-111: + SampleSquare(), the first two draws of the stream */
         Rng rng;
-        rng.seed = stream_seed(rc.rng_key, (uint32_t)pix, (uint32_t)(rc.sample_first + slot / rc.npix));
+        rng.seed = stream_seed(rc.rng_key, pix, (uint32_t)rc.sample_first + smp);
         rng.dim = 0u;
         fi = fi + (rng.next() - 0.5);
         fj = fj + (rng.next() - 0.5);
@@ -541,12 +542,14 @@ template <int CLS, bool PRIMARY>
 __device__ __forceinline__ void shade_vertex(const DevScene& S, const RenderConst& rc, const PathBuffers& pb, int bounce, int sort, int32_t slot,
                                              bool& want_shadow, bool& want_extend, uint32_t& key_shadow, uint32_t& key_extend) {
     /* ---- the vertex: hit, incoming ray, throughput, RNG dimension ---- */
+    uint32_t slot_smp, slot_pix; /* slot = sample_in_pass * npix + pixel */
+    rc.by_npix.divmod((uint32_t)slot, slot_smp, slot_pix);
     int32_t prim;
     double t, alpha, beta;
     d3 ro, rd, T;
     uint32_t dim;
     if (PRIMARY) {
-        const dd4 ph = ld256d(pb.primary + (slot % rc.npix)); /* written by the previous launch: read-only here */
+        const dd4 ph = ld256d(pb.primary + (uint32_t)slot_pix); /* written by the previous launch: read-only here */
         t = ph.v[0]; alpha = ph.v[1]; beta = ph.v[2];
         prim = (int32_t)unpack_lo(ph.v[3]);
     } else {
@@ -580,7 +583,7 @@ __device__ __forceinline__ void shade_vertex(const DevScene& S, const RenderCons
     const d3 wo = world_to_local(-rd, s);
 
     Rng rng;
-    rng.seed = stream_seed(rc.rng_key, (uint32_t)(slot % rc.npix), (uint32_t)(rc.sample_first + slot / rc.npix));
+    rng.seed = stream_seed(rc.rng_key, slot_pix, (uint32_t)rc.sample_first + slot_smp);
     rng.dim = dim;
 
     /* ---- next-event estimation (Camera.cpp:137-174) ---- */
@@ -664,11 +667,12 @@ __device__ __forceinline__ void shade_vertex(const DevScene& S, const RenderCons
 /* Queue position q of class CLS -> the path slot it names (-1 past the end). PRIMARY: the queue holds pixels and
  * position q means sample q / nq of pixel queue[q % nq] (sample-major: neighbouring positions, neighbouring records). */
 template <bool PRIMARY>
-__device__ __forceinline__ int32_t shade_entry(const int32_t* queue, int32_t nq, int32_t n, int32_t npix, int64_t q) {
+__device__ __forceinline__ int32_t shade_entry(const int32_t* queue, const FastDiv& by_nq, int32_t n, int32_t npix, int64_t q) {
     if (q >= (int64_t)n) return -1;
     if (PRIMARY) {
-        const int32_t s = (int32_t)q / nq;
-        return s * npix + __ldcg(queue + ((int32_t)q - s * nq));
+        uint32_t s, j;
+        by_nq.divmod((uint32_t)q, s, j);
+        return (int32_t)s * npix + __ldcg(queue + j);
     }
     return __ldcg(queue + q);
 }
@@ -707,7 +711,8 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
     int32_t base = __shfl_sync(FULL, a_raw, 0);
     if (base >= n) return;
     if (lane == 0) a_raw = atomicAdd(cursor, CH); /* the chunk after this one */
-    int32_t slot_next = shade_entry<PRIMARY>(queue, nq, n, rc.npix, (int64_t)base + lane);
+    const FastDiv by_nq = FastDiv::make((uint32_t)nq);
+    int32_t slot_next = shade_entry<PRIMARY>(queue, by_nq, n, rc.npix, (int64_t)base + lane);
     for (;;) {
         int32_t ns = 0, ne = 0;
         int32_t base_next = 0;
@@ -715,10 +720,10 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
         for (int k = 0; k < K; ++k) {
             const int32_t slot = slot_next;
             if (k + 1 < K) {
-                slot_next = shade_entry<PRIMARY>(queue, nq, n, rc.npix, (int64_t)base + (k + 1) * 32 + lane);
+                slot_next = shade_entry<PRIMARY>(queue, by_nq, n, rc.npix, (int64_t)base + (k + 1) * 32 + lane);
             } else {
                 base_next = __shfl_sync(FULL, a_raw, 0); /* issued a whole chunk ago */
-                slot_next = shade_entry<PRIMARY>(queue, nq, n, rc.npix, (int64_t)base_next + lane);
+                slot_next = shade_entry<PRIMARY>(queue, by_nq, n, rc.npix, (int64_t)base_next + lane);
             }
 #if PRT_SHADE_PREFETCH
             if (!PRIMARY && slot_next >= 0) {
@@ -736,7 +741,7 @@ __device__ __forceinline__ void shade_body(const DevScene& S, const RenderConst&
              * of the next iteration then starts two hops in */
             int32_t prim_next = -1;
             if (slot_next >= 0)
-                prim_next = PRIMARY ? __ldg(reinterpret_cast<const int32_t*>(pb.primary + (slot_next % rc.npix)) + 6)
+                prim_next = PRIMARY ? __ldg(reinterpret_cast<const int32_t*>(pb.primary + (slot_next - (int32_t)rc.by_npix.div((uint32_t)slot_next) * rc.npix)) + 6)
                                     : __ldcg(reinterpret_cast<const int32_t*>(rec_sector(pb, slot_next, 4)) + 6);
 #endif
             bool want_shadow = false, want_extend = false;

@@ -1,7 +1,8 @@
 /*
  * multi.cu — the render path on 1..8 GPUs of one box, behind the C ABI.
  *
- * The path shards with no exchange inside the loop: the scene is REPLICATED on every GPU, the samples of every
+ * The path shards with no exchange inside the loop: the scene is REPLICATED on every GPU (built once, copied GPU to
+ * GPU), the samples of every
  * pixel are split into contiguous ranges (the counter-based generator is keyed by (pixel, absolute sample index), so
  * the union of the shards is the one-GPU render), each GPU accumulates its range into its own FP64 frame, and ONE
  * collective — ncclReduce(sum, ncclDouble, W*H*3, root = devices[0]) over NVLink / NVSwitch — brings the frames
@@ -139,13 +140,18 @@ int prt_multi_create(const int32_t* devices, int32_t n, const prt_scene_desc* de
     m->ctx.assign((size_t)n, nullptr);
     m->scene.assign((size_t)n, nullptr);
     m->acc.assign((size_t)n, nullptr);
-    /* the scene is replicated: every GPU ingests, flattens and uploads its own copy, all at once */
-    int rc = on_every_gpu(n, [&](int g) {
-        int r = prt_context_create(m->devices[g], &m->ctx[g]);
-        if (r == PRT_OK) r = prt_scene_create(m->ctx[g], desc, &m->scene[g]);
-        if (r == PRT_OK) r = prt_scene_commit(m->scene[g], opts);
-        return r;
-    });
+    /* the scene is replicated: ingested, built and uploaded ONCE (devices[0]), then copied GPU to GPU on every other
+     * device at the same time (prt_scene_clone: peer copies over NVLink, no second host-side build, no n-fold host memory) */
+    int rc = prt_context_create(m->devices[0], &m->ctx[0]);
+    if (rc == PRT_OK) rc = prt_scene_create(m->ctx[0], desc, &m->scene[0]);
+    if (rc == PRT_OK) rc = prt_scene_commit(m->scene[0], opts);
+    if (rc == PRT_OK && n > 1)
+        rc = on_every_gpu(n, [&](int g) {
+            if (g == 0) return (int)PRT_OK;
+            int r = prt_context_create(m->devices[g], &m->ctx[g]);
+            if (r == PRT_OK) r = prt_scene_clone(m->scene[0], m->ctx[g], &m->scene[g]);
+            return r;
+        });
     if (rc != PRT_OK) { const std::string keep = prt_last_error(); prt_multi_destroy(m); return prt::set_error(rc, keep); }
     if (n > 1) {
         NcclApi& api = nccl_api();

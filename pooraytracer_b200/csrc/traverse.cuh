@@ -81,6 +81,19 @@ __device__ __forceinline__ double pack2(uint32_t lo, uint32_t hi) { return __hil
 __device__ __forceinline__ uint32_t unpack_lo(double v) { return (uint32_t)__double2loint(v); }
 __device__ __forceinline__ uint32_t unpack_hi(double v) { return (uint32_t)__double2hiint(v); }
 
+/* t = (D - n.o) / (n.d), Triangle.cpp:58 — the same IEEE quotient, without the divide's slow path for a ZERO dividend.
+ * A scattered or shadow ray starts ON a triangle, and the first leaf it visits holds that triangle and its coplanar
+ * neighbours: for an axis-aligned wall D - n.o is exactly 0 for about half of such rays (o.y = ro.y + rd.y t cancels to
+ * the last bit). CUDA's FP64 division handles a zero / denormal quotient in an out-of-line routine of ~65 instructions,
+ * run by the whole warp if one lane needs it: on cornell-box it ran once per two triangle tests, 6 % of k_extend's issued
+ * instructions (profiles/r2_s9_extend_hot_sass.txt). 0 / x for finite non-zero x is +-0 with the sign of the operands'
+ * signs' product: written out, it costs a compare. (NaN / inf denominators take the real division.) */
+__device__ __forceinline__ double plane_t(double num, double denom) {
+    if (num == 0.0 && fabs(denom) <= 1.7976931348623157e308)
+        return (__double2hiint(num) ^ __double2hiint(denom)) < 0 ? -0.0 : 0.0;
+    return num / denom;
+}
+
 /* Triangle::Hit. The 128-byte record is read as the plane (32 B) first and the remaining 96 B
  * only for candidates whose t is inside the interval. */
 __device__ __forceinline__ bool tri_test(const TriIsect* __restrict__ T, d3 o, d3 d, double tmin, double tmax,
@@ -91,7 +104,7 @@ __device__ __forceinline__ bool tri_test(const TriIsect* __restrict__ T, d3 o, d
     const d3 n = mk3(q0.v[0], q0.v[1], q0.v[2]);
     const double denom = dot(n, d);
     if (fabs(denom) < 1e-8) return false;
-    const double t = (q0.v[3] - dot(n, o)) / denom;
+    const double t = plane_t(q0.v[3] - dot(n, o), denom);
     if (!(tmin <= t && t <= tmax)) return false; /* Interval::Contains, inclusive */
     const dd4 q1 = ld256d(p + 32), q2 = ld256d(p + 64), q3 = ld256d(p + 96);
     const d3 w = mk3(q1.v[0], q1.v[1], q1.v[2]);
@@ -104,7 +117,7 @@ __device__ __forceinline__ bool tri_test(const TriIsect* __restrict__ T, d3 o, d
     const d3 n = mk3(q0.x, q0.y, q1.x);
     const double denom = dot(n, d);
     if (fabs(denom) < 1e-8) return false;
-    const double t = (q1.y - dot(n, o)) / denom;
+    const double t = plane_t(q1.y - dot(n, o), denom);
     if (!(tmin <= t && t <= tmax)) return false; /* Interval::Contains, inclusive */
     const double2 q2 = __ldg(p + 2), q3 = __ldg(p + 3), q4 = __ldg(p + 4), q5 = __ldg(p + 5), q6 = __ldg(p + 6), q7 = __ldg(p + 7);
     const d3 w = mk3(q2.x, q2.y, q3.x);

@@ -55,7 +55,7 @@ namespace prt {
  * the 10 M-triangle meshes below 30) spill to a local array, so depth is never lost; beyond PRT_SAH_STACK the
  * ray goes to the reference-order walk as before. */
 #ifndef PRT_SMEM_STACK
-#define PRT_SMEM_STACK 8
+#define PRT_SMEM_STACK 16
 #endif
 #define PRT_TRAVERSE_BLOCK 128 /* threads per block of every kernel that walks the tree */
 #define PRT_SMEM_STACK_WORDS (((PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) > 0 ? (PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) : 1) * PRT_TRAVERSE_BLOCK)
@@ -523,9 +523,24 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                         if (s0 == MISS) {
                             cur = sp > 0 ? PRT_POP() : PRT_DONE;
                         } else {
-                            if (s3 != MISS) PRT_PUSH(PRT_CHILD_OF(s3));
-                            if (s2 != MISS) PRT_PUSH(PRT_CHILD_OF(s2));
-                            if (s1 != MISS) PRT_PUSH(PRT_CHILD_OF(s1));
+                            /* the other hit children go on the stack farthest first. Validity is monotone in the sorted
+                             * keys (s1 valid if s2 is, s2 if s3 is), so with cnt of them valid the entries are
+                             * [s3 s2 s1], [s2 s1] or [s1]: three UNCONDITIONAL shared-memory stores (what lands above the new
+                             * stack pointer is never read) instead of three divergent push sites, which were 12 % of the
+                             * kernel's issued instructions at 3-6 active lanes (profiles/r2_s9_extend_hot_sass.txt) */
+                            const int cnt = (s1 != MISS ? 1 : 0) + (s2 != MISS ? 1 : 0) + (s3 != MISS ? 1 : 0);
+                            if (sp + 3 <= SM_N) {
+                                const int32_t c1 = PRT_CHILD_OF(s1), c2 = PRT_CHILD_OF(s2), c3 = PRT_CHILD_OF(s3);
+                                int32_t* top = sm + sp * PRT_TRAVERSE_BLOCK;
+                                top[0] = cnt == 3 ? c3 : (cnt == 2 ? c2 : c1);
+                                top[PRT_TRAVERSE_BLOCK] = cnt == 3 ? c2 : c1;
+                                top[2 * PRT_TRAVERSE_BLOCK] = c1;
+                                sp += cnt;
+                            } else { /* near the end of the shared part (or with a tiny test stack): one entry at a time */
+                                if (s3 != MISS) PRT_PUSH(PRT_CHILD_OF(s3));
+                                if (s2 != MISS) PRT_PUSH(PRT_CHILD_OF(s2));
+                                if (s1 != MISS) PRT_PUSH(PRT_CHILD_OF(s1));
+                            }
                             cur = PRT_CHILD_OF(s0);
                         }
 #undef PRT_CHILD_OF

@@ -43,6 +43,30 @@ def test_one_gpu_handle_is_the_single_gpu_path(gpu_ctx):
     assert np.array_equal(part, one.render(cam, make_params(6, 8, rng_key=4, spp_begin=2, spp_end=5)))
 
 
+def test_scene_clone_is_a_faithful_replica(gpu_ctx):
+    """prt_scene_clone (how prt_multi_create replicates the scene): device-to-device copies of every buffer, pointer table
+    rebound. On one GPU the replica lives in a second context of the same device; with more, on the last device. Same
+    image, same hits, bit for bit; the original may be destroyed first."""
+    from pooraytracer_b200 import Context
+    sc = cases.bathroom_small()  # textures, mirrors, several material classes
+    cam = make_camera(sc.camera, 48, 27)
+    prm = make_params(3, 8, rng_key=5)
+    for accel in (capi.ACCEL_SAH_BVH4, capi.ACCEL_LBVH4_DEVICE, capi.ACCEL_SAH_BVH4Q, capi.ACCEL_REFERENCE_BVH2):
+        one = Scene(gpu_ctx, sc, accel=accel)
+        want = one.render(cam, prm)
+        o, d = cases.ray_batch(sc)
+        want_hits = one.trace_closest(o, d)
+        ctx2 = Context(n_gpus() - 1)
+        rep = one.clone(ctx2)
+        one.close()
+        assert np.array_equal(rep.render(cam, prm), want), accel
+        for a, b in zip(rep.trace_closest(o, d), want_hits):
+            assert np.array_equal(a, b)
+        st = rep.stats()
+        assert st.n_triangles == sc.n_triangles and st.ref_stack_overflows == 0
+        rep.close()
+
+
 def test_bad_arguments_are_refused():
     sc = cases.tiny()
     with pytest.raises(Exception):

@@ -17,9 +17,9 @@ for k in extend shade shadow bath_extend rq10; do
   [ -f gpurun_out/${TAG}_$k.ncu-rep ] || continue
   ncu -i gpurun_out/${TAG}_$k.ncu-rep --page raw --csv 2>/dev/null | python tools/ncu_summary.py > gpurun_out/${TAG}_${k}_ncu_summary.txt
   ncu -i gpurun_out/${TAG}_$k.ncu-rep --page source --csv --print-source sass --launch-count 1 2>/dev/null | python tools/ncu_hot.py 60 > gpurun_out/${TAG}_${k}_hot_sass.txt
-  ncu -i gpurun_out/${TAG}_$k.ncu-rep --page source --csv --print-source cuda --launch-count 1 2>/dev/null > gpurun_out/${TAG}_${k}_src_raw.csv
+  ncu -i gpurun_out/${TAG}_$k.ncu-rep --page source --csv --print-source cuda,sass --launch-count 1 2>/dev/null > gpurun_out/${TAG}_${k}_src_raw.csv
   python tools/ncu_hot_src.py 60 < gpurun_out/${TAG}_${k}_src_raw.csv > gpurun_out/${TAG}_${k}_hot_src.txt 2>&1
-  head -c 200000 gpurun_out/${TAG}_${k}_src_raw.csv > gpurun_out/${TAG}_${k}_src_head.csv; rm -f gpurun_out/${TAG}_${k}_src_raw.csv
+  rm -f gpurun_out/${TAG}_${k}_src_raw.csv
 done
 rm -f gpurun_out/${TAG}_*.ncu-rep
 ls -la gpurun_out | tail -15
