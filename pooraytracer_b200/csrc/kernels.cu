@@ -229,7 +229,7 @@ struct AnyQueryPolicy {
 };
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
+__global__ void __launch_bounds__(PRT_TRAVERSE_BLOCK, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                        const double* __restrict__ tmin, const double* __restrict__ tmax,
                                                        int32_t* __restrict__ prim, double* __restrict__ t, double* __restrict__ alpha,
                                                        double* __restrict__ beta, const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_closest(
 }
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
+__global__ void __launch_bounds__(PRT_TRAVERSE_BLOCK, PRT_TRAVERSE_MIN_BLOCKS) k_trace_any(DevScene S, int64_t n, const double* __restrict__ o, const double* __restrict__ d,
                                                    const double* __restrict__ tmin, const double* __restrict__ tmax, uint8_t* __restrict__ hit,
                                                    const int32_t* __restrict__ order, int32_t* fetch, unsigned long long* counters) {
     __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
@@ -408,7 +408,7 @@ struct PrimaryPolicy {
 };
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_primary(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb) {
+__global__ void __launch_bounds__(PRT_TRAVERSE_BLOCK, PRT_TRAVERSE_MIN_BLOCKS) k_primary(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb) {
     __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     VisitCounters cnt = {0, 0, 0, 0, 0};
     PrimaryPolicy pol = {S, prim_class, rc, pb, pb.ctrl, {-1, 0, 0, 0}};
@@ -514,7 +514,7 @@ __device__ __forceinline__ void extend_body(const DevScene& S, const uint8_t* __
 }
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+__global__ void __launch_bounds__(PRT_TRAVERSE_BLOCK, PRT_TRAVERSE_MIN_BLOCKS) k_extend(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
     __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     VisitCounters cnt = {0, 0, 0, 0, 0};
     extend_body<COUNT, WIDE>(S, prim_class, rc, pb, bounce, sorted, cnt, sm_stack);
@@ -935,7 +935,7 @@ __device__ __forceinline__ void shadow_body(const DevScene& S, const RenderConst
 }
 
 template <bool COUNT, int WIDE>
-__global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
+__global__ void __launch_bounds__(PRT_TRAVERSE_BLOCK, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScene S, RenderConst rc, PathBuffers pb, int bounce, int sorted) {
     __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS];
     VisitCounters cnt = {0, 0, 0, 0, 0};
     shadow_body<COUNT, WIDE>(S, rc, pb, bounce, sorted, cnt, sm_stack);
@@ -953,7 +953,7 @@ __global__ void __launch_bounds__(128, PRT_TRAVERSE_MIN_BLOCKS) k_shadow(DevScen
 template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(128, 2) k_tail(DevScene S, const uint8_t* __restrict__ prim_class, RenderConst rc, PathBuffers pb, int first) {
     /* the stages are separated by grid-wide barriers: the traversal stack and the shade staging share one buffer */
-    __shared__ int32_t sm_stack[PRT_SMEM_STACK_WORDS > PRT_SHADE_STAGE_WORDS ? PRT_SMEM_STACK_WORDS : PRT_SHADE_STAGE_WORDS];
+    __shared__ int32_t sm_stack[PRT_STACK_WORDS_FOR(128) > PRT_SHADE_STAGE_WORDS ? PRT_STACK_WORDS_FOR(128) : PRT_SHADE_STAGE_WORDS];
     cg::grid_group grid = cg::this_grid();
     VisitCounters cnt = {0, 0, 0, 0, 0};
     for (int b = first; b <= rc.max_depth; ++b) {
@@ -1085,7 +1085,7 @@ static int persistent_grid(K kernel, int block, const LaunchConfig& lc, int64_t 
 #define PRT_DISPATCH_ONE(C, W, NAME, GRID, ARGS)      \
     do {                                              \
         auto KERNEL = NAME<C, W>;                     \
-        KERNEL<<<(GRID), 128, 0, st>>> ARGS;          \
+        KERNEL<<<(GRID), PRT_TRAVERSE_BLOCK, 0, st>>> ARGS;          \
     } while (0)
 /* wide: 2 = Node2 (or the reference tree), 4 = Node4, 40 = Node4Q */
 #define PRT_DISPATCH(count, wide, NAME, GRID, ARGS)                            \
@@ -1106,13 +1106,13 @@ void launch_trace_closest(const DevScene& S, int64_t n, const double* o, const d
                           int32_t* prim, double* t, double* alpha, double* beta, const int32_t* order, int32_t* fetch,
                           unsigned long long* counters, const LaunchConfig& lc, cudaStream_t st) {
     if (n <= 0) return;
-    PRT_DISPATCH(counters != nullptr, wide_of(S), k_trace_closest, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, prim, t, alpha, beta, order, fetch, counters));
+    PRT_DISPATCH(counters != nullptr, wide_of(S), k_trace_closest, persistent_grid(KERNEL, PRT_TRAVERSE_BLOCK, lc, n), (S, n, o, d, tmin, tmax, prim, t, alpha, beta, order, fetch, counters));
 }
 void launch_trace_any(const DevScene& S, int64_t n, const double* o, const double* d, const double* tmin, const double* tmax,
                       uint8_t* hit, const int32_t* order, int32_t* fetch, unsigned long long* counters, const LaunchConfig& lc,
                       cudaStream_t st) {
     if (n <= 0) return;
-    PRT_DISPATCH(counters != nullptr, wide_of(S), k_trace_any, persistent_grid(KERNEL, 128, lc, n), (S, n, o, d, tmin, tmax, hit, order, fetch, counters));
+    PRT_DISPATCH(counters != nullptr, wide_of(S), k_trace_any, persistent_grid(KERNEL, PRT_TRAVERSE_BLOCK, lc, n), (S, n, o, d, tmin, tmax, hit, order, fetch, counters));
 }
 void launch_query_sort(int64_t n, const double* o, const double* d, const float* key_lo, const float* key_scale, uint16_t* keys,
                        int32_t* hist, int32_t* cursor, int32_t* order, const LaunchConfig& lc, cudaStream_t st) {
@@ -1162,8 +1162,8 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         if (!primary && lc.tail_paths > 0 && expect < (double)lc.tail_paths) break;
         const int sort = lc.sort_min > 0 && expect >= (double)lc.sort_min ? 1 : 0;
         if (ev) cudaEventRecord(ev[4 * b], st);
-        if (primary) PRT_DISPATCH(count, wide, k_primary, persistent_grid(KERNEL, 128, lc, rc.npix), (S, prim_class, rc, pb));
-        else PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, prim_class, rc, pb, b, sorted));
+        if (primary) PRT_DISPATCH(count, wide, k_primary, persistent_grid(KERNEL, PRT_TRAVERSE_BLOCK, lc, rc.npix), (S, prim_class, rc, pb));
+        else PRT_DISPATCH(count, wide, k_extend, persistent_grid(KERNEL, PRT_TRAVERSE_BLOCK, lc, rc.n_paths), (S, prim_class, rc, pb, b, sorted));
         ++launches;
         if (ev) cudaEventRecord(ev[4 * b + 1], st);
         if (primary) {
@@ -1187,7 +1187,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
         }
         if (ev) cudaEventRecord(ev[4 * b + 2], st);
         if (rc.sample_lights) {
-            PRT_DISPATCH(count, wide, k_shadow, persistent_grid(KERNEL, 128, lc, rc.n_paths), (S, rc, pb, b, sort));
+            PRT_DISPATCH(count, wide, k_shadow, persistent_grid(KERNEL, PRT_TRAVERSE_BLOCK, lc, rc.n_paths), (S, rc, pb, b, sort));
             ++launches;
         }
         sorted = sort;

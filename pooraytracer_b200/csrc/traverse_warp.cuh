@@ -57,8 +57,13 @@ namespace prt {
 #ifndef PRT_SMEM_STACK
 #define PRT_SMEM_STACK 16
 #endif
-#define PRT_TRAVERSE_BLOCK 128 /* threads per block of every kernel that walks the tree */
-#define PRT_SMEM_STACK_WORDS (((PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) > 0 ? (PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) : 1) * PRT_TRAVERSE_BLOCK)
+#ifndef PRT_TRAVERSE_BLOCK
+#define PRT_TRAVERSE_BLOCK 128 /* threads per block of the kernels that walk the tree (k_tail: always 128); the stack's stride is blockDim.x.
+                                  Registers are per SM sub-partition (16 K each): 6 warps per sub-partition = 80 registers, 5 = 96, whatever the
+                                  block size, so smaller blocks buy no in-between budget (ptxas: 32 x 23 and 64 x 11 still compile to 80) */
+#endif
+#define PRT_STACK_WORDS_FOR(threads) (((PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) > 0 ? (PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK) : 1) * (threads))
+#define PRT_SMEM_STACK_WORDS PRT_STACK_WORDS_FOR(PRT_TRAVERSE_BLOCK)
 
 /* refill idle lanes once fewer than this many lanes hold a ray (Policy::REFILL_BELOW). Refilling early keeps
  * lanes busy; refilling late keeps the rays of a warp (and the path vertices they push for k_shade) together.
@@ -265,17 +270,18 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
     const unsigned lt_mask = (1u << lane) - 1u;
     constexpr int SM_N = PRT_SMEM_STACK < PRT_SAH_STACK ? PRT_SMEM_STACK : PRT_SAH_STACK;
     constexpr int LOC_N = PRT_SAH_STACK - SM_N > 0 ? PRT_SAH_STACK - SM_N : 1;
-    int32_t* const sm = sm_stack + threadIdx.x; /* entry e of this lane: sm[e * PRT_TRAVERSE_BLOCK] */
+    const int BS = blockDim.x;
+    int32_t* const sm = sm_stack + threadIdx.x; /* entry e of this lane: sm[e * blockDim.x] */
     int32_t deep[LOC_N];                        /* entries SM_N .. PRT_SAH_STACK - 1 (rarely reached) */
     int sp = 0;
 #define PRT_PUSH(v)                                                     \
     do {                                                                \
-        if (sp < SM_N) sm[sp * PRT_TRAVERSE_BLOCK] = (v);               \
+        if (sp < SM_N) sm[sp * BS] = (v);               \
         else if (sp < PRT_SAH_STACK) deep[sp - SM_N] = (v);             \
         else { overflow = true; break; }                                \
         ++sp;                                                           \
     } while (0)
-#define PRT_POP() (--sp, sp < SM_N ? sm[sp * PRT_TRAVERSE_BLOCK] : deep[sp - SM_N])
+#define PRT_POP() (--sp, sp < SM_N ? sm[sp * BS] : deep[sp - SM_N])
     int32_t cur = PRT_DONE;
     int32_t leaf = -1; /* PRT_WALK_MODE 1: parked leaf, (slot << 3) | (triangles left - 1) */
     int32_t slot = -1;
@@ -531,10 +537,10 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, P& pol, i
                             const int cnt = (s1 != MISS ? 1 : 0) + (s2 != MISS ? 1 : 0) + (s3 != MISS ? 1 : 0);
                             if (sp + 3 <= SM_N) {
                                 const int32_t c1 = PRT_CHILD_OF(s1), c2 = PRT_CHILD_OF(s2), c3 = PRT_CHILD_OF(s3);
-                                int32_t* top = sm + sp * PRT_TRAVERSE_BLOCK;
+                                int32_t* top = sm + sp * BS;
                                 top[0] = cnt == 3 ? c3 : (cnt == 2 ? c2 : c1);
-                                top[PRT_TRAVERSE_BLOCK] = cnt == 3 ? c2 : c1;
-                                top[2 * PRT_TRAVERSE_BLOCK] = c1;
+                                top[BS] = cnt == 3 ? c2 : c1;
+                                top[2 * BS] = c1;
                                 sp += cnt;
                             } else { /* near the end of the shared part (or with a tiny test stack): one entry at a time */
                                 if (s3 != MISS) PRT_PUSH(PRT_CHILD_OF(s3));
