@@ -55,9 +55,10 @@ WORKLOADS = {
     "veach-mis": dict(width=1280, height=720, depth=100, total_spp=12000),
     "bathroom2": dict(width=1280, height=720, depth=50, total_spp=500),
 }
-ACCELS = {"bvh4": "ACCEL_SAH_BVH4", "bvh2": "ACCEL_SAH_BVH2", "lbvh": "ACCEL_LBVH4_DEVICE", "bvh4q": "ACCEL_SAH_BVH4Q"}
+ACCELS = {"bvh4": "ACCEL_SAH_BVH4", "bvh2": "ACCEL_SAH_BVH2", "lbvh": "ACCEL_LBVH4_DEVICE", "bvh4q": "ACCEL_SAH_BVH4Q", "auto": "ACCEL_AUTO"}
 ACCEL_TEXT = {"bvh4": "SAH BVH4 (128 B nodes", "bvh2": "SAH BVH2 (64 B nodes", "lbvh": "device-built LBVH4 (128 B nodes",
-              "bvh4q": "SAH BVH4, 8-bit quantised child boxes (64 B nodes"}
+              "bvh4q": "SAH BVH4, 8-bit quantised child boxes (64 B nodes",
+              "auto": "SAH BVH4, layout chosen by mesh size (FP32 128 B nodes below 262144 triangles, 8-bit quantised 64 B nodes from there up"}
 
 
 def parse():
@@ -74,7 +75,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip every host-CPU leg")
     ap.add_argument("--headline-only", action="store_true", help="only the headline workload: no scenes / rayquery / job sub-objects (A/B runs, ncu)")
     ap.add_argument("--no-rayquery-10m", action="store_true", help="skip the 10 M-triangle ray-query rows (their host-side builds take ~1 min)")
-    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=list(ACCELS))
+    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "auto"), choices=list(ACCELS))
     ap.add_argument("--cpu-spp", type=int, default=0,
                     help="spp of the bounded CPU sample (0 = 12 for the cpu_baseline of the b200 arm, about 13 s of 16 host cores on the default workload; 2 per step for --impl reference)")
     ap.add_argument("--max-leaf", type=int, default=0, help="triangles per BVH leaf (0 = the library's default, 4)")

@@ -121,7 +121,13 @@ enum prt_accel {
     /* PRT_ACCEL_SAH_BVH4 with the child boxes quantised to 8 bits per plane relative to the node
      * (64-byte nodes: half the bytes per node fetch, slightly looser boxes, more decode arithmetic).
      * Same hits: the decoded boxes contain the boxes they replace. */
-    PRT_ACCEL_SAH_BVH4Q = 4
+    PRT_ACCEL_SAH_BVH4Q = 4,
+    /* Let the library choose between the two SAH BVH4 layouts by mesh size: quantised 64-byte nodes
+     * from 262144 triangles up (the node set no longer fits the caches the FP32 nodes are served
+     * from: measured +4 % on the 1.1 M-triangle bathroom stand-in, profiles/r2_s11_accel_ab.txt),
+     * FP32 128-byte nodes below (measured +1..3 % on cornell-box / veach-mis). prt_get_stats reports
+     * the layout that was built. Same hits either way. */
+    PRT_ACCEL_AUTO = 5
 };
 
 typedef struct prt_build_opts {

@@ -28,6 +28,7 @@ ACCEL_SAH_BVH2 = 1
 ACCEL_SAH_BVH4 = 2
 ACCEL_LBVH4_DEVICE = 3
 ACCEL_SAH_BVH4Q = 4
+ACCEL_AUTO = 5
 
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2

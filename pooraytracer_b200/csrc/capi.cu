@@ -366,7 +366,8 @@ void prt_scene_destroy(prt_scene* scene) {
 
 int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
     if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_scene_commit: null scene");
-    const int accel = opts ? opts->accel : PRT_ACCEL_SAH_BVH2;
+    int accel = opts ? opts->accel : PRT_ACCEL_SAH_BVH2;
+    if (accel == PRT_ACCEL_AUTO) accel = s->host.n_tris >= 262144 ? PRT_ACCEL_SAH_BVH4Q : PRT_ACCEL_SAH_BVH4;
     if (accel != PRT_ACCEL_REFERENCE_BVH2 && accel != PRT_ACCEL_SAH_BVH2 && accel != PRT_ACCEL_SAH_BVH4 && accel != PRT_ACCEL_LBVH4_DEVICE && accel != PRT_ACCEL_SAH_BVH4Q)
         return fail(PRT_ERR_UNSUPPORTED, "prt_scene_commit: unknown accel");
     HostScene& h = s->host;

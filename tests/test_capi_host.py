@@ -92,6 +92,16 @@ def test_bad_descriptions_are_rejected(built):
         Scene(Context(-1), bad)
 
 
+def test_accel_auto_picks_by_mesh_size(built):
+    """PRT_ACCEL_AUTO: 128-byte FP32 nodes for small meshes, 64-byte quantised ones from 262144 triangles up."""
+    small = Scene(Context(-1), cases.tiny(), accel=capi.ACCEL_AUTO)
+    assert small.stats().node_bytes == 128
+    big = scenes.terrain(400, 330)
+    assert big.n_triangles >= 262144
+    assert Scene(Context(-1), big, accel=capi.ACCEL_AUTO).stats().node_bytes == 64
+    assert Scene(Context(-1), big, accel=capi.ACCEL_SAH_BVH4).stats().node_bytes == 128
+
+
 def test_empty_scene_host(built):
     empty = scenes.SceneData(name="empty", vertices=np.zeros((0, 3, 3)), texcoords=None, mesh_first=np.zeros(1, np.int64),
                              mesh_material=np.zeros(0, np.int32), mesh_names=[], materials=[], textures=[], camera=cases.tiny().camera)

@@ -10,7 +10,7 @@ $M --log-file gpurun_out/${TAG}_launches_cornell-box.csv python bench.py --steps
 $M --log-file gpurun_out/${TAG}_launches_veach-mis.csv python bench.py --scene veach-mis --steps 1 --warmup 1 --no-cpu-baseline --headline-only > gpurun_out/${TAG}_ncu_l2.log 2>&1; echo "launchlist veach rc=$?"
 $M --log-file gpurun_out/${TAG}_launches_bathroom2.csv python bench.py --scene bathroom2 --steps 1 --warmup 1 --no-cpu-baseline --headline-only > gpurun_out/${TAG}_ncu_l3.log 2>&1; echo "launchlist bathroom rc=$?"
 for s in cornell-box veach-mis bathroom2; do
-  python tools/traffic_from_launches.py gpurun_out/${TAG}_launches_$s.csv profiles/${TAG}_launches_$s.csv $s bvh4 64 > gpurun_out/${TAG}_traffic_$s.json
+  python tools/traffic_from_launches.py gpurun_out/${TAG}_launches_$s.csv profiles/${TAG}_launches_$s.csv $s auto 64 > gpurun_out/${TAG}_traffic_$s.json
 done
 TAG=$TAG bash tools/ncu_captures.sh
 N="ncu --set full --clock-control none --import-source on"

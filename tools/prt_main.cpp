@@ -3,7 +3,7 @@
  * loads <dir>/<name>.{obj,mtl,xml}, renders on 1..8 B200s of the box, writes <out>.png and <out>.hdr.
  *
  *   prt_main <scene-dir> <name> [--spp N] [--depth N] [--rr P] [--no-nee] [--out PATH] [--gpus N | --devices a,b,..]
- *            [--device K] [--strtod] [--seed KEY] [--accel bvh2|bvh4|bvh4q|lbvh]
+ *            [--device K] [--strtod] [--seed KEY] [--accel auto|bvh2|bvh4|bvh4q|lbvh]
  *
  * Defaults are main.cpp's: spp 100, depth 100, Russian roulette 0.8, light sampling on, black background. The scene is
  * replicated on every GPU, the samples are split across them, one NCCL reduce brings the frame to the first GPU
@@ -34,11 +34,11 @@ static double seconds_since(std::chrono::steady_clock::time_point t) {
 
 int main(int argc, char** argv) {
     if (argc < 3) {
-        std::fprintf(stderr, "usage: %s <scene-dir> <name> [--spp N] [--depth N] [--rr P] [--no-nee] [--out PATH] [--gpus N | --devices a,b,..] [--device K] [--strtod] [--seed KEY] [--accel bvh2|bvh4|bvh4q|lbvh]\n", argv[0]);
+        std::fprintf(stderr, "usage: %s <scene-dir> <name> [--spp N] [--depth N] [--rr P] [--no-nee] [--out PATH] [--gpus N | --devices a,b,..] [--device K] [--strtod] [--seed KEY] [--accel auto|bvh2|bvh4|bvh4q|lbvh]\n", argv[0]);
         return 2;
     }
     const std::string dir = argv[1], name = argv[2];
-    int spp = 100, depth = 100, nee = 1, accel = PRT_ACCEL_SAH_BVH4;
+    int spp = 100, depth = 100, nee = 1, accel = PRT_ACCEL_AUTO;
     double rr = 0.8;
     unsigned long long seed = 0;
     uint32_t flags = 0;
@@ -70,7 +70,7 @@ int main(int argc, char** argv) {
         else if (!std::strcmp(argv[i], "--chunk")) (void)next("--chunk"); /* accepted for old command lines: passes are cut by the library */
         else if (!std::strcmp(argv[i], "--accel")) {
             const std::string a = next("--accel");
-            accel = a == "bvh2" ? PRT_ACCEL_SAH_BVH2 : a == "bvh4q" ? PRT_ACCEL_SAH_BVH4Q : a == "lbvh" ? PRT_ACCEL_LBVH4_DEVICE : PRT_ACCEL_SAH_BVH4;
+            accel = a == "bvh2" ? PRT_ACCEL_SAH_BVH2 : a == "bvh4q" ? PRT_ACCEL_SAH_BVH4Q : a == "lbvh" ? PRT_ACCEL_LBVH4_DEVICE : a == "bvh4" ? PRT_ACCEL_SAH_BVH4 : PRT_ACCEL_AUTO;
         } else { std::fprintf(stderr, "unknown option %s\n", argv[i]); return 2; }
     }
     if (spp < 1 || devices.empty() || devices.size() > 8) { std::fprintf(stderr, "--spp must be positive, 1..8 GPUs\n"); return 2; }
