@@ -252,6 +252,25 @@ int prt_trace_closest_device(prt_scene* scene, int64_t n, const double* origins,
 int prt_trace_any_device(prt_scene* scene, int64_t n, const double* origins,
                          const double* directions, const double* tmin, const double* tmax,
                          uint8_t* hit, void* stream);
+/* prt_trace_closest_device that allocates NOTHING: no cudaMalloc, cudaFree or allocating library
+ * routine on any call, the first included. No counterpart in the reference: added
+ * for callers that cannot reach cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it). Same kernels, same results bit for bit; the
+ * scratch the kernels need (the work cursor of the persistent traversal kernel and, under
+ * PRT_SORT_MIN, the ray-binning keys / order / histogram) lives in one static device array of
+ * 6.25 MiB that every GPU which loads the library holds until exit.
+ *   - n > PRT_NOALLOC_MAX_RAYS is refused with PRT_ERR_INVALID_ARGUMENT (split the batch);
+ *   - n == 0 performs the once-per-device set-up only (the address look-up of the array), which a
+ *     caller can do before a capture begins;
+ *   - every call on a GPU shares the one array: calls that OVERLAP on the same GPU (two streams,
+ *     two scenes, two threads) race on it. Serialise them, or use prt_trace_closest_device, whose
+ *     scratch is per scene;
+ *   - the scene's prt_stats are not touched (no timing events, no fetch counters). */
+#define PRT_NOALLOC_MAX_RAYS 1048576
+int prt_trace_closest_device_noalloc(prt_scene* scene, int64_t n, const double* origins,
+                                     const double* directions, const double* tmin,
+                                     const double* tmax, int32_t* prim, double* t, double* alpha,
+                                     double* beta, void* stream);
 
 /* ---- light sampling: replaces Hittable::Sample on `lights` (Source/Hittable.h:36) -------------- */
 /* u: [n][4] uniforms in draw order (HittableList.h:49, BVH.cpp:64, Triangle.cpp:86 x then y).

@@ -29,6 +29,7 @@ ACCEL_SAH_BVH4 = 2
 ACCEL_LBVH4_DEVICE = 3
 ACCEL_SAH_BVH4Q = 4
 ACCEL_AUTO = 5
+NOALLOC_MAX_RAYS = 1048576  # PRT_NOALLOC_MAX_RAYS
 
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
@@ -149,6 +150,7 @@ PROTOTYPES = {
     "prt_trace_any": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 5),
     "prt_trace_closest_device": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 9),
     "prt_trace_any_device": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 6),
+    "prt_trace_closest_device_noalloc": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 9),
     "prt_sample_lights": (C.c_int, [C.c_void_p, C.c_int64] + [C.c_void_p] * 7),
     "prt_render": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p]),
     "prt_render_device": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p, C.c_void_p]),

@@ -932,3 +932,73 @@ int prt_synchronize(prt_context* ctx) {
 }
 
 }  // extern "C"
+
+/* ---- the entry point that allocates nothing -----------------------------------------------------
+ * prt_trace_closest_device for callers that may not reach cudaMalloc (CUDA graph capture, serving
+ * loops, harnesses that forbid it). Same kernels, same launch rules; the scratch they need — the work
+ * cursor of the persistent traversal kernel and, when PRT_SORT_MIN asks for ray binning, the keys,
+ * the binned order, the histogram and the bin cursors — lives in ONE file-scope device array instead
+ * of the scene's cudaMalloc'ed buffers. Every GPU that loads the library holds the array until exit.
+ * g_noalloc_scratch below is a host-side stand-in in host code: its device address comes from
+ * cudaGetSymbolAddress, once per device, with that device current. */
+#define PRT_NOALLOC_ALIGN(x) (((x) + 255) / 256 * 256)
+#define PRT_NOALLOC_OFF_FETCH 0
+#define PRT_NOALLOC_OFF_HIST 256
+#define PRT_NOALLOC_OFF_CURSOR (PRT_NOALLOC_OFF_HIST + PRT_NOALLOC_ALIGN(sizeof(int32_t) * PRT_KEY_BINS))
+#define PRT_NOALLOC_OFF_ORDER (PRT_NOALLOC_OFF_CURSOR + PRT_NOALLOC_ALIGN(sizeof(int32_t) * PRT_KEY_BINS))
+#define PRT_NOALLOC_OFF_KEYS (PRT_NOALLOC_OFF_ORDER + PRT_NOALLOC_ALIGN(sizeof(int32_t) * PRT_NOALLOC_MAX_RAYS))
+#define PRT_NOALLOC_BYTES (PRT_NOALLOC_OFF_KEYS + PRT_NOALLOC_ALIGN(sizeof(uint16_t) * PRT_NOALLOC_MAX_RAYS))
+#define PRT_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PRT_NOALLOC_BYTES]; /* 6.25 MiB for 2^20 rays */
+
+namespace {
+/* device address of g_noalloc_scratch on the CURRENT device (the caller made `device` current) */
+int noalloc_scratch(int device, unsigned char** out) {
+    static std::mutex mu;
+    static unsigned char* address[PRT_NOALLOC_MAX_DEVICES] = {nullptr};
+    if (device < 0 || device >= PRT_NOALLOC_MAX_DEVICES) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_closest_device_noalloc: device index beyond 63");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!address[device]) {
+        unsigned char* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) return fail(PRT_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        address[device] = p;
+    }
+    *out = address[device];
+    return PRT_OK;
+}
+}  // namespace
+
+extern "C" int prt_trace_closest_device_noalloc(prt_scene* s, int64_t n, const double* o, const double* d, const double* tmin,
+                                                const double* tmax, int32_t* prim, double* t, double* alpha, double* beta,
+                                                void* stream) {
+    int rc = need_device(s);
+    if (rc) return rc;
+    if (n < 0) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_closest_device_noalloc: negative ray count");
+    if (n > PRT_NOALLOC_MAX_RAYS)
+        return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_closest_device_noalloc: " + std::to_string((long long)n) + " rays in one call, the static scratch holds at most " +
+                                                  std::to_string((long long)PRT_NOALLOC_MAX_RAYS) + " (PRT_NOALLOC_MAX_RAYS): split the batch or call prt_trace_closest_device");
+    if (n > 0 && (!o || !d || !tmin || !tmax || !prim)) return fail(PRT_ERR_INVALID_ARGUMENT, "prt_trace_closest_device_noalloc: null array");
+    unsigned char* scratch = nullptr;
+    rc = noalloc_scratch(s->ctx->device, &scratch); /* n == 0: the set-up alone (e.g. before a graph capture starts) */
+    if (rc || n == 0) return rc;
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->ctx->stream;
+    int32_t* fetch = (int32_t*)(scratch + PRT_NOALLOC_OFF_FETCH);
+    /* the array keeps what the previous call left: the cursor must start at zero */
+    CUDA_TRY(cudaMemsetAsync(fetch, 0, 4 * sizeof(int32_t), st));
+    const LaunchConfig lc = launch_config(s->ctx);
+    const int32_t* order = nullptr;
+    if (lc.sort_min > 0 && n >= lc.sort_min) { /* the rule of query_order() */
+        int32_t* hist = (int32_t*)(scratch + PRT_NOALLOC_OFF_HIST);
+        int32_t* cursor = (int32_t*)(scratch + PRT_NOALLOC_OFF_CURSOR);
+        int32_t* binned = (int32_t*)(scratch + PRT_NOALLOC_OFF_ORDER);
+        uint16_t* keys = (uint16_t*)(scratch + PRT_NOALLOC_OFF_KEYS);
+        CUDA_TRY(cudaMemsetAsync(hist, 0, sizeof(int32_t) * PRT_KEY_BINS, st)); /* launch_query_sort wants it zero on entry */
+        launch_query_sort(n, o, d, s->key_lo, s->key_scale, keys, hist, cursor, binned, lc, st);
+        order = binned;
+    }
+    launch_trace_closest(s->dev, n, o, d, tmin, tmax, prim, t, alpha, beta, order, fetch, nullptr, lc, st);
+    CUDA_TRY(cudaGetLastError());
+    return PRT_OK;
+}
