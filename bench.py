@@ -260,7 +260,9 @@ def ncu_evidence(scene, accel, S, width, height, depth, ms_per_step_per_gpu, pea
         lj = json.load(open(os.path.join(ROOT, "profiles", "r2_limiters.json"))).get(scene)
         if lj:
             out.update({"limiter": lj["limiter"], "l1tex_pct": lj["l1tex_pct"], "simd_lanes": lj["simd_lanes"], "issue_active_pct": lj["issue_active_pct"],
-                        "dram_pct_ncu": lj["dram_pct"], "limiter_source": lj["source"]})
+                        "dram_pct_ncu": lj["dram_pct"], "limiter_source": lj["source"],
+                        # `bound` above names the denominator (HBM peak, GB/s); this names what ncu shows the kernel waiting on
+                        "bound_ncu": "l1tex" if lj["l1tex_pct"] >= 70.0 else "latency"})
     except Exception:
         pass
     return out
@@ -636,6 +638,13 @@ def run_b200(a):
                 for tris_m in (1,) if a.no_rayquery_10m else (1, 10):
                     for mesh in ("terrain", "soup"):
                         rq += measure_rayquery(a, tris_m, mesh, cpu_prefix=cpu_prefix if tris_m == 1 else 0)
+                try:  # what ncu names for the one ray-query case that was captured (tools/ncu_captures.sh: terrain-10M, first closest launch)
+                    lj = json.load(open(os.path.join(ROOT, "profiles", "r2_limiters.json"))).get("rayquery-terrain-10M")
+                    for row in rq:
+                        if lj and row["case"].startswith("terrain-10000000 random closest"):
+                            row["ncu"] = {k: lj[k] for k in ("limiter", "l1tex_pct", "dram_pct", "l2_pct", "issue_active_pct", "simd_lanes", "source")}
+                except Exception:
+                    pass
                 line["rayquery"] = rq
                 line["rayquery_note"] = ("2^24 rays, device-resident, one GPU, CUDA-event time of the kernel; cpu_baseline / oracle_check on the 1 M-triangle meshes "
                                          "(the reference's BVH over 10 M triangles takes minutes to build: not inside the bench); 2/4/8-GPU figures: tools/rayquery_multi.sh")

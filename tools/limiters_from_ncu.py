@@ -32,12 +32,16 @@ def main():
         l1, dram, issue = m["l1tex__throughput.avg.pct_of_peak_sustained_active"], m["gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"], m["smsp__issue_active.avg.pct_of_peak_sustained_active"]
         ceilings = {"l1tex throughput": l1, "dram throughput": dram, "issue slots": issue, "l2 throughput": m.get("lts__throughput.avg.pct_of_peak_sustained_elapsed", 0.0)}
         top = max(ceilings, key=ceilings.get)
-        out[scene] = {
-            "limiter": f"{top} ({ceilings[top]:.0f} % of peak) with dependent-fetch latency behind it: long-scoreboard stalls "
-                       f"{m['smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio']:.1f} of {m['smsp__average_warp_latency_per_inst_issued.ratio']:.1f} cycles per issue, "
-                       f"{m['sm__warps_active.avg.pct_of_peak_sustained_active']:.0f} % warp occupancy",
-            "l1tex_pct": l1, "dram_pct": dram, "issue_active_pct": issue, "l2_pct": ceilings["l2 throughput"],
-            "simd_lanes": m["smsp__thread_inst_executed_per_inst_executed.ratio"], "source": path}
+        ls, lat = m['smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio'], m['smsp__average_warp_latency_per_inst_issued.ratio']
+        occ = m['sm__warps_active.avg.pct_of_peak_sustained_active']
+        if ceilings[top] >= 70.0:
+            text = (f"{top} ({ceilings[top]:.0f} % of peak) with dependent-fetch latency behind it: long-scoreboard stalls "
+                    f"{ls:.1f} of {lat:.1f} cycles per issue, {occ:.0f} % warp occupancy")
+        else:  # no throughput unit is near its ceiling: the walk waits on its own dependent fetches
+            text = (f"dependent-fetch latency: long-scoreboard stalls {ls:.1f} of {lat:.1f} cycles per issue at {occ:.0f} % warp occupancy; "
+                    f"nearest throughput ceiling {top} at {ceilings[top]:.0f} % of peak")
+        out[scene] = {"limiter": text, "l1tex_pct": l1, "dram_pct": dram, "issue_active_pct": issue, "l2_pct": ceilings["l2 throughput"],
+                      "simd_lanes": m["smsp__thread_inst_executed_per_inst_executed.ratio"], "warp_occupancy_pct": occ, "source": path}
     print(json.dumps(out, indent=1))
 
 

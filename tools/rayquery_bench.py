@@ -30,7 +30,7 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--check", type=int, default=0, help="compare the first N rays with the CPU oracle")
     ap.add_argument("--max-leaf", type=int, default=0)
-    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "bvh4"), choices=["bvh2", "bvh4", "lbvh", "bvh4q"])
+    ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "auto"), choices=["auto", "bvh2", "bvh4", "lbvh", "bvh4q"])
     a = ap.parse_args()
     import torch
     from pooraytracer_b200 import Context, Scene, _capi as capi, scenes
@@ -55,7 +55,7 @@ def main():
     t0 = time.time()
     import ctypes as C
     o_ = capi.PrtBuildOpts()
-    o_.accel = {"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE, "bvh4q": capi.ACCEL_SAH_BVH4Q}[a.accel]
+    o_.accel = {"bvh4": capi.ACCEL_SAH_BVH4, "bvh2": capi.ACCEL_SAH_BVH2, "lbvh": capi.ACCEL_LBVH4_DEVICE, "bvh4q": capi.ACCEL_SAH_BVH4Q, "auto": capi.ACCEL_AUTO}[a.accel]
     o_.reserved[0] = a.max_leaf
     rc = scene.lib.prt_scene_commit(scene.handle, C.byref(o_))
     assert rc == 0, scene.lib.prt_last_error()
@@ -113,8 +113,10 @@ def main():
             alg = nodes * st.node_bytes + tris * st.tri_bytes
             line = {"case": f"{a.mesh}-{sc.n_triangles} {kind} {query}", "n_gpus": world, "rays": n_tot, "mrays_s": n_tot / ms / 1e3, "ms": ms,
                     "nodes_per_ray": nodes / n_tot, "tris_per_ray": tris / n_tot, "bytes_per_ray": alg / n_tot,
-                    "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s",
-                                 "frac": alg / (ms * 1e-3) / 1e9 / (peak * world)},
+                    # cache-oblivious demand (every node / triangle fetch counted as if it came from HBM) against the HBM peak:
+                    # above 1 on coherent batches, where L1 / L2 serve the fetches; the limiter ncu names is in profiles/r2_limiters.json
+                    "algorithmic_gb_s": alg / (ms * 1e-3) / 1e9, "hbm_peak_gb_s": peak * world,
+                    "algorithmic_demand_vs_hbm": alg / (ms * 1e-3) / 1e9 / (peak * world), "accel": a.accel, "node_bytes": st.node_bytes,
                     "hit_fraction": hits / n_tot,
                     "scene_create_s": t_create, "scene_commit_s": t_commit, "n_nodes": st.n_nodes, "build_ms": st.build_ms}
             if a.check and query == "closest" and kind == "random":

@@ -45,7 +45,7 @@ def main():
     counted = max([len(v) for k, v in ids.items() if k.startswith("k_tail<1")] + [0])
     out = {}
     for k in sorted(per):
-        if re.match(r"k_\w+<1", k):
+        if re.match(r"k_(extend|shadow|tail|trace\w*|primary)<1", k):  # the counting instantiations (k_shade's first parameter is the material class)
             continue
         # kernels without the COUNT template parameter (shade, accumulate) also ran in the instrumented step
         n = steps if re.match(r"k_(extend|shadow|tail|trace|primary)", k) else steps + counted
