@@ -12,7 +12,8 @@ pooraytracer_b200/scenes.py in the reference's material vocabulary.
              ranks; under torchrun every rank renders its own sample range of the step and ONE NCCL reduce per step
              sums the float64 accumulators on rank 0 (inside the timed region)
   e2e        the same through the C ABI a user calls — prt_multi_render on all N GPUs of the box from one process, HOST
-             image out: sample sharding, the ncclReduce to the first GPU and the device-to-host copy are all inside the
+             image out: sample sharding, the reduction of the frames on the first GPU (peer loads over NVLink; NCCL where the GPUs
+             cannot address each other) and the device-to-host copy are all inside the
              timed region; `image_checksum` is of a fixed 64-sample range and is the same for every N (1e-13)
   roofline   the traversal kernels (k_extend + k_shadow): `achieved` = algorithmic bytes (BVH nodes x node bytes +
              triangles x 128 B actually fetched, counted by an instrumented run of the same step) / their summed
@@ -292,7 +293,7 @@ def roofline_object(st0, rays0, stage, n_stage, stage_rays, scene, accel, S, wid
 # ---------------------------------------------------------------------------------------------------------------------
 def measure_box(box, sc, scene_name, a, n_gpus, width, height, depth, total_spp, steps, warmup, want_roofline=True):
     """prt_multi_render on all GPUs of `box`. A step = S spp per GPU (S * n_gpus samples split across the GPUs, one
-    ncclReduce): `value` without a host image, `e2e` with one (pinned), both wall-clock around synchronous calls."""
+    reduction on the first GPU): `value` without a host image, `e2e` with one (pinned), both wall-clock around synchronous calls."""
     import torch
     from pooraytracer_b200 import _capi as capi, make_camera, make_params
     cam = make_camera(sc.camera, width, height)
@@ -349,7 +350,7 @@ def measure_box(box, sc, scene_name, a, n_gpus, width, height, depth, total_spp,
     out["e2e"] = {"value": e2e_steps * S * n_gpus / dte, "unit": "spp/s", "h2d_bytes_per_step": C.sizeof(cam) + C.sizeof(fixed),
                   "d2h_bytes_per_step": npix * 3 * 8, "steps": e2e_steps, "pageable_host_image_value": S * n_gpus / dtp,
                   "image_checksum": float(host.sum().item()), "checksum_of": "samples [0, 64) of the frame, reduced on the first GPU: the same for every N up to the order of the final FP64 additions",
-                  "call": f"prt_multi_render on {n_gpus} GPU(s): sample split, ncclReduce to the first GPU and the device-to-host copy inside the timed region"}
+                  "call": f"prt_multi_render on {n_gpus} GPU(s): sample split, reduction of the frames to the first GPU ({box.reduce_kind}) and the device-to-host copy inside the timed region"}
     if want_roofline:
         n_stage = min(2, steps)
         ext = shd = sdw = 0.0
@@ -392,8 +393,8 @@ def measure_rayquery(a, tris_m, mesh, n_log2=24, reps=3, cpu_prefix=0):
         tmin = torch.full((n,), 1e-4, dtype=torch.float64, device="cuda")
         tmax = torch.full((n,), float("inf"), dtype=torch.float64, device="cuda")
         prim = torch.empty(n, dtype=torch.int32, device="cuda")
-        t = torch.empty(n, dtype=torch.float64, device="cuda")
-        al, be = torch.empty_like(t), torch.empty_like(t)
+        t = torch.zeros(n, dtype=torch.float64, device="cuda")  # a miss leaves t / alpha / beta untouched (0, as the CPU answer has them)
+        al, be = torch.zeros_like(t), torch.zeros_like(t)
         hit = torch.empty(n, dtype=torch.uint8, device="cuda")
         tmax_any = torch.from_numpy(tmax_any_h).cuda()
         tmin_any = torch.full((n,), 1e-3, dtype=torch.float64, device="cuda")
@@ -430,7 +431,10 @@ def measure_rayquery(a, tris_m, mesh, n_log2=24, reps=3, cpu_prefix=0):
                 if query == "closest":  # gate 1 on this very batch: the prefix bit-exact against the CPU answer
                     m = cpu["rays"]
                     got = (prim[:m].cpu().numpy(), t[:m].cpu().numpy(), al[:m].cpu().numpy(), be[:m].cpu().numpy())
-                    row["oracle_check"] = {"rays": m, "bit_exact": bool(all(np.array_equal(x, y) for x, y in zip(got, want)))}
+                    same = [bool(np.array_equal(x, y)) for x, y in zip(got, want)]
+                    row["oracle_check"] = {"rays": m, "bit_exact": all(same), "hits": int((want[0] >= 0).sum())}
+                    if not all(same):
+                        row["oracle_check"]["differs_in"] = [nm for nm, ok in zip(("prim", "t", "alpha", "beta"), same) if not ok]
             rows.append(row)
         del do, dd, tmin, tmax, prim, t, al, be, hit, tmax_any, tmin_any
     scene.close()
@@ -455,7 +459,7 @@ def measure_jobs(a, n_gpus):
             line = [l for l in r.stdout.splitlines() if l.startswith("job:")]
             jobs["cornell-box spp=3000 depth=100 1024x1024"] = {
                 "wall_s": wall, "ok": r.returncode == 0 and os.path.exists(os.path.join(d, "out.png")), "n_gpus": n_gpus,
-                "what": "prt_main (drop-in for main.cpp): load OBJ/MTL/XML -> build + upload on every GPU -> render, samples split -> ncclReduce -> resolve -> PNG + HDR; process start to exit",
+                "what": "prt_main (drop-in for main.cpp): load OBJ/MTL/XML -> build + upload on every GPU -> render, samples split -> frames reduced on the first GPU -> resolve -> PNG + HDR; process start to exit",
                 "phases": line[0][5:].strip() if line else r.stderr[-300:], "reference_published_s": 20382.22}
     # (2) north_star: "bathroom2 at 500 spp / depth 50 rendered in seconds on 8 GPUs"
     sc = make_scene("bathroom2")
@@ -476,7 +480,7 @@ def measure_jobs(a, n_gpus):
     st, reduce_ms = box.stats()
     jobs["bathroom2 spp=500 depth=50 1280x720"] = {
         "wall_s": t_build + t_render + t_out, "n_gpus": n_gpus, "triangles": sc.n_triangles,
-        "what": "arrays -> prt_multi_create (ingest + SAH build + upload on every GPU) -> prt_multi_render (samples split, ncclReduce, host image) -> prt_multi_resolve -> PNG + HDR",
+        "what": "arrays -> prt_multi_create (ingest + SAH build + upload on every GPU) -> prt_multi_render (samples split, frames reduced on the first GPU, host image) -> prt_multi_resolve -> PNG + HDR",
         "build_upload_s": t_build, "render_reduce_s": t_render, "resolve_write_s": t_out, "reduce_ms": reduce_ms,
         "spp_per_s": 500 / t_render, "mrays_s": (st.extend_rays + st.shadow_rays) / t_render / 1e6}
     box.close()

@@ -309,14 +309,20 @@ int prt_resolve_thresholds(double* out254);
  * Replaces main.cpp:36-52 for a caller that wants every GPU of the node: the scene is replicated (ingested, built and
  * uploaded ONCE, on devices[0], then copied GPU to GPU: prt_scene_clone), Camera::Render's samples are split into contiguous ranges across the GPUs
  * (the generator is keyed by the absolute sample index, so the union of the shards is the one-GPU image up to the order
- * of the final FP64 additions), and ONE collective — ncclReduce(sum, double, W*H*3) to devices[0] over NVLink — ends
- * the render. The library owns the communicator; NCCL is bound at run time and only when n > 1. Used from one host
- * thread at a time; the library runs one thread of its own per GPU. */
+ * of the final FP64 additions), and ONE reduction of the W*H*3 FP64 frames to devices[0] over NVLink ends the render:
+ * where devices[0] can address the other GPUs' memory (every NVSwitch box) a kernel on devices[0] reads the other frames
+ * through peer loads and adds them in device order — no communicator, nothing to initialise, bit-reproducible; otherwise
+ * ncclReduce(sum, double) on communicators the library owns (NCCL is bound at run time, only then). The environment
+ * variable PRT_MULTI_REDUCE=peer|nccl forces one kind. Used from one host thread at a time; the library runs one thread
+ * of its own per GPU. */
 typedef struct prt_multi prt_multi;
+enum prt_reduce_kind { PRT_REDUCE_NONE = 0 /* one GPU */, PRT_REDUCE_NCCL = 1, PRT_REDUCE_PEER = 2 };
 int prt_multi_create(const int32_t* devices, int32_t n, const prt_scene_desc* desc, const prt_build_opts* opts,
                      prt_multi** out);
 void prt_multi_destroy(prt_multi* multi);
 int prt_multi_device_count(const prt_multi* multi);
+/* prt_reduce_kind of this handle */
+int prt_multi_reduce_kind(const prt_multi* multi);
 /* Camera::Render on all GPUs: rgb (host, W*H*3 doubles, may be NULL) is OVERWRITTEN with the reduced image of the sample
  * range, scaled by 1/samples_per_pixel; the reduced accumulators also stay on devices[0] for prt_multi_resolve. */
 int prt_multi_render(prt_multi* multi, const prt_camera* camera, const prt_render_params* params, double* rgb);
@@ -324,7 +330,7 @@ int prt_multi_render(prt_multi* multi, const prt_camera* camera, const prt_rende
  * reduce, as the reference scrubs the final pixel. */
 int prt_multi_resolve(prt_multi* multi, uint8_t* rgb8, float* rgb32f);
 /* Sums of the per-GPU counters of the last call, gpu_ms = the slowest GPU's device time; reduce_ms (may be NULL) = device
- * time of the collective on devices[0]. */
+ * time of the reduction on devices[0]. */
 int prt_multi_get_stats(const prt_multi* multi, prt_stats* out, double* reduce_ms);
 /* Hittable::Hit over a batch split into contiguous ray ranges, one per GPU; no collective. Host pointers. */
 int prt_multi_trace_closest(prt_multi* multi, int64_t n, const double* origins, const double* directions,

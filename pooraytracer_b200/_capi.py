@@ -30,6 +30,7 @@ ACCEL_LBVH4_DEVICE = 3
 ACCEL_SAH_BVH4Q = 4
 ACCEL_AUTO = 5
 NOALLOC_MAX_RAYS = 1048576  # PRT_NOALLOC_MAX_RAYS
+REDUCE_NONE, REDUCE_NCCL, REDUCE_PEER = 0, 1, 2  # prt_reduce_kind
 
 RENDER_EXACT_VISIBILITY = 1
 RENDER_COUNTERS = 2
@@ -163,6 +164,7 @@ PROTOTYPES = {
     "prt_multi_create": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(PrtSceneDesc), C.POINTER(PrtBuildOpts), C.POINTER(C.c_void_p)]),
     "prt_multi_destroy": (None, [C.c_void_p]),
     "prt_multi_device_count": (C.c_int, [C.c_void_p]),
+    "prt_multi_reduce_kind": (C.c_int, [C.c_void_p]),
     "prt_multi_render": (C.c_int, [C.c_void_p, C.POINTER(PrtCamera), C.POINTER(PrtRenderParams), C.c_void_p]),
     "prt_multi_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "prt_multi_get_stats": (C.c_int, [C.c_void_p, C.POINTER(PrtStats), C.POINTER(C.c_double)]),

@@ -349,8 +349,8 @@ class Scene:
 
 
 class MultiScene:
-    """prt_multi: one scene replicated on several GPUs of the box, samples sharded, one NCCL reduce (harness mirror of
-    include/prt_b200.h's prt_multi_* calls)."""
+    """prt_multi: one scene replicated on several GPUs of the box, samples sharded, one reduction of the frames to the
+    first GPU (peer loads over NVLink, or NCCL: `reduce_kind`). Harness mirror of include/prt_b200.h's prt_multi_* calls."""
 
     def __init__(self, devices, data, accel: int = capi.ACCEL_SAH_BVH4, max_leaf: int = 0):
         self.lib = capi.load_library()
@@ -368,6 +368,10 @@ class MultiScene:
             del keep
         self.handle = h
         self.n = len(devs)
+
+    @property
+    def reduce_kind(self) -> str:
+        return {capi.REDUCE_NONE: "none", capi.REDUCE_NCCL: "nccl", capi.REDUCE_PEER: "peer"}[self.lib.prt_multi_reduce_kind(self.handle)]
 
     def close(self):
         if getattr(self, "handle", None):

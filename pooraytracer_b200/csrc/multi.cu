@@ -5,20 +5,31 @@
  * GPU), the samples of every
  * pixel are split into contiguous ranges (the counter-based generator is keyed by (pixel, absolute sample index), so
  * the union of the shards is the one-GPU render), each GPU accumulates its range into its own FP64 frame, and ONE
- * collective — ncclReduce(sum, ncclDouble, W*H*3, root = devices[0]) over NVLink / NVSwitch — brings the frames
- * together. NaN scrub and the sRGB quantiser run on the root AFTER the reduce, as the reference scrubs the final
- * pixel (Camera.cpp:291-293). One host thread per GPU issues that GPU's launches; the library owns the
- * communicator. Ray-query batches are split into contiguous ray ranges with no collective at all.
+ * reduction to devices[0] brings the frames together. NaN scrub and the sRGB quantiser run on the root AFTER the
+ * reduce, as the reference scrubs the final pixel (Camera.cpp:291-293). One host thread per GPU issues that GPU's
+ * launches. Ray-query batches are split into contiguous ray ranges with no collective at all.
+ *
+ * The reduction comes in two kinds (prt_multi_reduce_kind; PRT_MULTI_REDUCE=peer|nccl overrides the choice):
+ *   PEER  where devices[0] can address every other GPU's memory (NVLink / NVSwitch: every B200 box): ONE kernel on the
+ *         root, k_sum_peers, reads the other frames through peer loads and adds them to its own in the fixed order
+ *         g = 1, 2, ... (bit-reproducible from run to run, which a ring's or tree's order is not), stream-ordered behind
+ *         every GPU's last pass by one event per GPU. W*H*3 doubles per peer cross the switch once (7 x 25 MB for a
+ *         1024^2 frame on 8 GPUs: 0.3 ms). No communicator: a handle is ready as soon as the scene is (ncclCommInitAll
+ *         on 8 GPUs costs 3.5 s, and again at exit: measured, profiles/r2_s15_bench_n8.json; a 3000-spp cornell-box job
+ *         renders in 0.5 s on the same box);
+ *   NCCL  otherwise: ncclReduce(sum, ncclDouble, root = devices[0]), grouped, one communicator per GPU owned by the
+ *         handle. Bound at run time (dlopen of libnccl.so.2, the system's or the one a host process already loaded):
+ *         a one-GPU or PEER handle never touches it, and libprt_b200.so carries no link-time dependency on it.
  *
  * Replaces, for a C / C++ caller: main.cpp:36-52 (build world / lights, Camera::Render, WriteColorAttachment) on a
- * whole box. NCCL is bound at run time (dlopen of libnccl.so.2, the system's or the one a host process already
- * loaded): a one-GPU handle never touches it, and libprt_b200.so itself carries no link-time dependency on it.
+ * whole box.
  */
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <nccl.h>
 
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -73,6 +84,32 @@ void split_range(int64_t begin, int64_t end, int g, int n, int64_t* b, int64_t* 
     *e = *b + base + (g < extra ? 1 : 0);
 }
 
+/* PEER reduction: root[i] += frame_1[i] + ... in that order; frames are other GPUs' memory read over NVLink. Eight
+ * independent 16-byte loads in flight per thread and pass; the grid is sized by the caller (a multiple of the SM count). */
+struct PeerFrames {
+    const double* frame[7];
+    int n;
+};
+__global__ void __launch_bounds__(256) k_sum_peers(double* __restrict__ root, PeerFrames f, size_t count) {
+    const size_t pairs = count / 2, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += stride) {
+        double2 a = reinterpret_cast<double2*>(root)[i];
+        double2 b[7];
+#pragma unroll
+        for (int g = 0; g < 7; ++g)
+            if (g < f.n) b[g] = reinterpret_cast<const double2*>(f.frame[g])[i];
+#pragma unroll
+        for (int g = 0; g < 7; ++g)
+            if (g < f.n) { a.x += b[g].x; a.y += b[g].y; }
+        reinterpret_cast<double2*>(root)[i] = a;
+    }
+    if ((count & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+        double a = root[count - 1];
+        for (int g = 0; g < f.n; ++g) a += f.frame[g][count - 1];
+        root[count - 1] = a;
+    }
+}
+
 struct Worker {
     int rc = PRT_OK;
     std::string error;
@@ -105,7 +142,9 @@ struct prt_multi {
     std::vector<prt_scene*> scene;
     std::vector<double*> acc; /* per GPU: W*H*3 FP64 accumulators */
     size_t acc_n = 0;
-    std::vector<ncclComm_t> comms;
+    std::vector<ncclComm_t> comms;       /* PRT_REDUCE_NCCL */
+    std::vector<cudaEvent_t> frame_done; /* PRT_REDUCE_PEER: per GPU, recorded behind its last pass */
+    int reduce_kind = PRT_REDUCE_NONE;
     int32_t width = 0, height = 0;
     bool rendered = false;
     double reduce_ms = 0.0;
@@ -121,6 +160,8 @@ void prt_multi_destroy(prt_multi* m) {
     if (m->ev0) { cudaSetDevice(m->devices[0]); cudaEventDestroy(m->ev0); cudaEventDestroy(m->ev1); }
     for (ncclComm_t c : m->comms)
         if (c) nccl_api().CommDestroy(c);
+    for (int g = 0; g < (int)m->frame_done.size(); ++g)
+        if (m->frame_done[g]) { cudaSetDevice(m->devices[g]); cudaEventDestroy(m->frame_done[g]); }
     for (prt_scene* s : m->scene) prt_scene_destroy(s);
     for (prt_context* c : m->ctx) prt_context_destroy(c);
     delete m;
@@ -141,28 +182,73 @@ int prt_multi_create(const int32_t* devices, int32_t n, const prt_scene_desc* de
     m->scene.assign((size_t)n, nullptr);
     m->acc.assign((size_t)n, nullptr);
     /* the scene is replicated: ingested, built and uploaded ONCE (devices[0]), then copied GPU to GPU on every other
-     * device at the same time (prt_scene_clone: peer copies over NVLink, no second host-side build, no n-fold host memory) */
+     * device at the same time (prt_scene_clone: peer copies over NVLink, no second host-side build, no n-fold host memory).
+     * The other GPUs' contexts come up on their own threads WHILE the host builds the tree for the first. */
+    std::vector<int> ctx_rc((size_t)n, PRT_OK);
+    std::vector<std::string> ctx_err((size_t)n);
+    std::vector<std::thread> bring_up;
+    for (int g = 1; g < n; ++g)
+        bring_up.emplace_back([&, g] {
+            ctx_rc[g] = prt_context_create(m->devices[g], &m->ctx[g]);
+            if (ctx_rc[g] != PRT_OK) ctx_err[g] = prt_last_error();
+        });
     int rc = prt_context_create(m->devices[0], &m->ctx[0]);
     if (rc == PRT_OK) rc = prt_scene_create(m->ctx[0], desc, &m->scene[0]);
     if (rc == PRT_OK) rc = prt_scene_commit(m->scene[0], opts);
-    if (rc == PRT_OK && n > 1)
-        rc = on_every_gpu(n, [&](int g) {
-            if (g == 0) return (int)PRT_OK;
-            int r = prt_context_create(m->devices[g], &m->ctx[g]);
-            if (r == PRT_OK) r = prt_scene_clone(m->scene[0], m->ctx[g], &m->scene[g]);
-            return r;
-        });
-    if (rc != PRT_OK) { const std::string keep = prt_last_error(); prt_multi_destroy(m); return prt::set_error(rc, keep); }
+    std::string first_error = rc != PRT_OK ? prt_last_error() : "";
+    for (auto& t : bring_up) t.join();
+    for (int g = 1; g < n && rc == PRT_OK; ++g)
+        if (ctx_rc[g] != PRT_OK) { rc = ctx_rc[g]; first_error = "GPU " + std::to_string(g) + ": " + ctx_err[g]; }
+    if (rc == PRT_OK && n > 1) {
+        rc = on_every_gpu(n, [&](int g) { return g == 0 ? (int)PRT_OK : prt_scene_clone(m->scene[0], m->ctx[g], &m->scene[g]); });
+        if (rc != PRT_OK) first_error = prt_last_error();
+    }
+    if (rc != PRT_OK) { prt_multi_destroy(m); return prt::set_error(rc, first_error); }
     if (n > 1) {
-        NcclApi& api = nccl_api();
-        if (!api.ok()) { prt_multi_destroy(m); return prt::set_error(PRT_ERR_UNSUPPORTED, "prt_multi_create: " + api.error); }
-        m->comms.assign((size_t)n, nullptr);
-        const ncclResult_t r = api.CommInitAll(m->comms.data(), n, m->devices.data());
-        if (r != ncclSuccess) {
-            const std::string msg = std::string("ncclCommInitAll: ") + api.GetErrorString(r);
-            m->comms.clear();
+        /* which reduction: peer loads where the root can address every other GPU, NCCL otherwise */
+        const char* want = std::getenv("PRT_MULTI_REDUCE");
+        const bool force_nccl = want && !std::strcmp(want, "nccl"), force_peer = want && !std::strcmp(want, "peer");
+        bool peer_ok = !force_nccl;
+        for (int g = 1; g < n && peer_ok; ++g) {
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, m->devices[0], m->devices[g]) != cudaSuccess || !can) peer_ok = false;
+        }
+        if (force_peer && !peer_ok) {
             prt_multi_destroy(m);
-            return prt::set_error(PRT_ERR_CUDA, msg);
+            return prt::set_error(PRT_ERR_UNSUPPORTED, "prt_multi_create: PRT_MULTI_REDUCE=peer, but the first device cannot address every other device's memory");
+        }
+        if (peer_ok) {
+            cudaSetDevice(m->devices[0]);
+            for (int g = 1; g < n; ++g) {
+                const cudaError_t e = cudaDeviceEnablePeerAccess(m->devices[g], 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError(); /* a host process (torch) got there first */
+                else if (e != cudaSuccess) {
+                    const std::string msg = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e);
+                    prt_multi_destroy(m);
+                    return prt::set_error(PRT_ERR_CUDA, msg);
+                }
+            }
+            m->frame_done.assign((size_t)n, nullptr);
+            for (int g = 1; g < n; ++g) {
+                cudaSetDevice(m->devices[g]);
+                if (cudaEventCreateWithFlags(&m->frame_done[g], cudaEventDisableTiming) != cudaSuccess) {
+                    prt_multi_destroy(m);
+                    return prt::set_error(PRT_ERR_CUDA, "prt_multi_create: cudaEventCreate failed");
+                }
+            }
+            m->reduce_kind = PRT_REDUCE_PEER;
+        } else {
+            NcclApi& api = nccl_api();
+            if (!api.ok()) { prt_multi_destroy(m); return prt::set_error(PRT_ERR_UNSUPPORTED, "prt_multi_create: " + api.error); }
+            m->comms.assign((size_t)n, nullptr);
+            const ncclResult_t r = api.CommInitAll(m->comms.data(), n, m->devices.data());
+            if (r != ncclSuccess) {
+                const std::string msg = std::string("ncclCommInitAll: ") + api.GetErrorString(r);
+                m->comms.clear();
+                prt_multi_destroy(m);
+                return prt::set_error(PRT_ERR_CUDA, msg);
+            }
+            m->reduce_kind = PRT_REDUCE_NCCL;
         }
     }
     cudaSetDevice(m->devices[0]);
@@ -175,6 +261,7 @@ int prt_multi_create(const int32_t* devices, int32_t n, const prt_scene_desc* de
 }
 
 int prt_multi_device_count(const prt_multi* m) { return m ? m->n : 0; }
+int prt_multi_reduce_kind(const prt_multi* m) { return m ? m->reduce_kind : PRT_REDUCE_NONE; }
 
 int prt_multi_render(prt_multi* m, const prt_camera* camera, const prt_render_params* params, double* rgb) {
     if (!m || !camera || !params) return prt::set_error(PRT_ERR_INVALID_ARGUMENT, "prt_multi_render: null argument");
@@ -207,10 +294,27 @@ int prt_multi_render(prt_multi* m, const prt_camera* camera, const prt_render_pa
         p.spp_end = (int32_t)e;
         return prt_render_device(m->scene[g], camera, &p, m->acc[g], nullptr);
     });
+    if (rc == PRT_OK && m->reduce_kind == PRT_REDUCE_PEER)
+        for (int g = 1; g < m->n; ++g) { /* this GPU's frame is complete behind this point of its stream */
+            cudaSetDevice(m->devices[g]);
+            if (cudaEventRecord(m->frame_done[g], m->ctx[g]->stream) != cudaSuccess) return prt::set_error(PRT_ERR_CUDA, "prt_multi_render: cudaEventRecord failed");
+        }
     if (rc != PRT_OK) return rc;
     cudaSetDevice(m->devices[0]);
     cudaEventRecord(m->ev0, m->ctx[0]->stream);
-    if (m->n > 1) {
+    if (m->reduce_kind == PRT_REDUCE_PEER) {
+        /* THE exchange step: one kernel on the root reads every other frame over NVLink, behind every GPU's last pass */
+        PeerFrames f;
+        f.n = m->n - 1;
+        for (int g = 1; g < m->n; ++g) {
+            f.frame[g - 1] = m->acc[g];
+            if (cudaStreamWaitEvent(m->ctx[0]->stream, m->frame_done[g], 0) != cudaSuccess) return prt::set_error(PRT_ERR_CUDA, "prt_multi_render: cudaStreamWaitEvent failed");
+        }
+        cudaEventRecord(m->ev0, m->ctx[0]->stream); /* reduce_ms = the kernel alone, not the wait for the slowest GPU */
+        const size_t want = (count / 2 + 255) / 256, cap = (size_t)m->ctx[0]->sm_count * 8;
+        k_sum_peers<<<(unsigned)(want < cap ? (want ? want : 1) : cap), 256, 0, m->ctx[0]->stream>>>(m->acc[0], f, count);
+        if (cudaGetLastError() != cudaSuccess) return prt::set_error(PRT_ERR_CUDA, "prt_multi_render: k_sum_peers failed to launch");
+    } else if (m->reduce_kind == PRT_REDUCE_NCCL) {
         /* THE collective: stream-ordered behind every GPU's last pass, in place on the root */
         NcclApi& api = nccl_api();
         ncclResult_t r = api.GroupStart();

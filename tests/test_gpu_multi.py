@@ -1,5 +1,6 @@
 """The whole-box layer behind the C ABI (prt_multi_*, pooraytracer_b200/csrc/multi.cu): scene replicated,
-samples sharded in C++, ONE ncclReduce(sum, double) to the first GPU, output stage after the reduce. Runs on however many GPUs
+samples sharded in C++, ONE reduction of the FP64 frames to the first GPU (peer loads over NVLink by default, ncclReduce
+under PRT_MULTI_REDUCE=nccl: both are run), output stage after the reduce. Runs on however many GPUs
 the box shows: with one, the handle must be the single-GPU path bit for bit; with more, the reduced image equals the one-GPU
 image up to the order of the final FP64 additions (TOLERANCE: 1e-13 relative), and ray-query batches split into contiguous
 ranges return the one-GPU answers exactly. Replaces /root/reference/main.cpp:36-52 for a C / C++ caller."""
@@ -27,6 +28,7 @@ def test_one_gpu_handle_is_the_single_gpu_path(gpu_ctx):
     prm = make_params(6, 8, rng_key=4)
     one = Scene(gpu_ctx, sc, accel=capi.ACCEL_SAH_BVH4)
     box = MultiScene([0], sc)
+    assert box.reduce_kind == "none"
     img = box.render(cam, prm)
     assert np.array_equal(img, one.render(cam, prm))
     st, reduce_ms = box.stats()
@@ -77,17 +79,21 @@ def test_bad_arguments_are_refused():
         MultiScene([99], sc)
 
 
+@pytest.mark.parametrize("kind", ["peer", "nccl"])
 @pytest.mark.parametrize("spp", [1, 5, 16])
-def test_all_visible_gpus_reduce_to_the_one_gpu_image(gpu_ctx, spp):
-    """spp 1: more GPUs than samples (the idle ones only join the reduce); 5: uneven slices; 16: even"""
+def test_all_visible_gpus_reduce_to_the_one_gpu_image(gpu_ctx, spp, kind, monkeypatch):
+    """spp 1: more GPUs than samples (the idle ones only join the reduce); 5: uneven slices; 16: even.
+    kind: k_sum_peers on the first GPU (the default on an NVLink box) or ncclReduce."""
     n = n_gpus()
     if n < 2:
-        pytest.skip("one GPU visible: the NCCL reduce needs two")
+        pytest.skip("one GPU visible: a reduce needs two")
+    monkeypatch.setenv("PRT_MULTI_REDUCE", kind)
     sc = cases.cornell_small()
     cam = make_camera(sc.camera, 96, 96)
     prm = make_params(spp, 10, rng_key=11)
     one = Scene(gpu_ctx, sc, accel=capi.ACCEL_SAH_BVH4).render(cam, prm)
     box = MultiScene(list(range(n)), sc)
+    assert box.reduce_kind == kind
     img = box.render(cam, prm)
     assert np.allclose(img, one, rtol=1e-13, atol=1e-15)
     st, reduce_ms = box.stats()
@@ -95,6 +101,24 @@ def test_all_visible_gpus_reduce_to_the_one_gpu_image(gpu_ctx, spp):
     rgb8, _ = box.resolve(96, 96)
     assert (rgb8 == Scene(gpu_ctx, sc).resolve(one)[0]).mean() > 0.9999
     # determinism of the reduce
+    assert np.array_equal(box.render(cam, prm), img)
+
+
+def test_default_reduce_is_peer_loads_and_odd_frames_work(gpu_ctx, monkeypatch):
+    """without PRT_MULTI_REDUCE an NVLink box gets the peer-load kernel (no communicator to initialise); a frame with an
+    odd number of doubles (5 x 3 x 3) exercises the kernel's scalar tail"""
+    n = n_gpus()
+    if n < 2:
+        pytest.skip("one GPU visible")
+    monkeypatch.delenv("PRT_MULTI_REDUCE", raising=False)
+    sc = cases.tiny()
+    box = MultiScene(list(range(n)), sc)
+    assert box.reduce_kind == "peer"
+    cam = make_camera(sc.camera, 5, 3)
+    prm = make_params(2 * n + 1, 6, rng_key=3)
+    one = Scene(gpu_ctx, sc, accel=capi.ACCEL_SAH_BVH4).render(cam, prm)
+    img = box.render(cam, prm)
+    assert np.allclose(img, one, rtol=1e-13, atol=1e-15)
     assert np.array_equal(box.render(cam, prm), img)
 
 

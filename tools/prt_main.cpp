@@ -6,7 +6,7 @@
  *            [--device K] [--strtod] [--seed KEY] [--accel auto|bvh2|bvh4|bvh4q|lbvh]
  *
  * Defaults are main.cpp's: spp 100, depth 100, Russian roulette 0.8, light sampling on, black background. The scene is
- * replicated on every GPU, the samples are split across them, one NCCL reduce brings the frame to the first GPU
+ * replicated on every GPU, the samples are split across them, one reduction (peer loads over NVLink, or NCCL) brings the frame to the first GPU
  * (prt_multi_render), where the output stage of Camera::WriteColorAttachment runs (prt_multi_resolve). The library
  * cuts a GPU's sample range into wavefront passes itself.
  */

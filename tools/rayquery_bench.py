@@ -74,8 +74,8 @@ def main():
         tmin = torch.full((n,), 1e-4, dtype=torch.float64, device="cuda")
         tmax = torch.full((n,), float("inf"), dtype=torch.float64, device="cuda")
         prim = torch.empty(n, dtype=torch.int32, device="cuda")
-        t = torch.empty(n, dtype=torch.float64, device="cuda")
-        al, be = torch.empty_like(t), torch.empty_like(t)
+        t = torch.zeros(n, dtype=torch.float64, device="cuda")  # a miss leaves t / alpha / beta untouched
+        al, be = torch.zeros_like(t), torch.zeros_like(t)
         hit = torch.empty(n, dtype=torch.uint8, device="cuda")
         tmax_any = torch.from_numpy(np.ascontiguousarray((scenes.hash_uniform(n_all, 5, 1) * diag)[lo_:hi_])).cuda()
         tmin_any = torch.full((n,), 1e-3, dtype=torch.float64, device="cuda")
