@@ -576,6 +576,58 @@ inline void set_child_box(float* lo, float* hi, const Box6& b) {
 
 }  // namespace
 
+/* Tree rotations (Kensler 2008) on the finished binary tree: at every inner node, exchanging one child with a grandchild
+ * on the other side leaves the node's own box as it is and changes ONE box, the other child's; the exchange that shrinks
+ * that box most is applied if it shrinks it at all. Subtrees move whole, so every box stays the exact union of its
+ * leaves. Post-order, a few passes. PRT_SAH_ROTATE = number of passes (experiments; 0 = off). */
+static int rotate_tree(std::vector<TmpNode>& t, int passes) {
+    std::vector<int32_t> order, stack;
+    stack.push_back(0);
+    while (!stack.empty()) { /* pre-order, reversed below: children before parents */
+        const int32_t n = stack.back();
+        stack.pop_back();
+        if (t[n].left < 0) continue;
+        order.push_back(n);
+        stack.push_back(t[n].left);
+        stack.push_back(t[n].right);
+    }
+    int applied = 0;
+    auto merged_area = [&](int32_t a, int32_t b) {
+        Box6 u = t[a].box;
+        box_grow(u, t[b].box);
+        return half_area(u);
+    };
+    for (int pass = 0; pass < passes; ++pass) {
+        int changed = 0;
+        for (size_t k = order.size(); k-- > 0;) {
+            TmpNode& N = t[order[k]];
+            int best_side = -1, best_opt = 0;
+            double best_gain = 0.0;
+            for (int side = 0; side < 2; ++side) {
+                const int32_t c = side ? N.right : N.left, other = side ? N.left : N.right;
+                if (t[c].left < 0) continue;
+                const double a_c = half_area(t[c].box);
+                const double g0 = a_c - merged_area(other, t[c].right); /* other <-> c.left  */
+                const double g1 = a_c - merged_area(t[c].left, other);  /* other <-> c.right */
+                if (g0 > best_gain) { best_gain = g0; best_side = side; best_opt = 0; }
+                if (g1 > best_gain) { best_gain = g1; best_side = side; best_opt = 1; }
+            }
+            if (best_side < 0) continue;
+            const int32_t c = best_side ? N.right : N.left;
+            int32_t& other_slot = best_side ? N.left : N.right;
+            int32_t& grand_slot = best_opt ? t[c].right : t[c].left;
+            if (!(best_gain > 1e-12 * half_area(t[c].box))) continue;
+            std::swap(other_slot, grand_slot);
+            t[c].box = t[t[c].left].box;
+            box_grow(t[c].box, t[t[c].right].box);
+            ++changed;
+        }
+        applied += changed;
+        if (!changed) break;
+    }
+    return applied;
+}
+
 /* binned-SAH binary tree over all triangles (TmpNode[0] = root) + the permuted index array */
 static void build_sah_tree(HostScene& s, int n_threads, int max_leaf, std::vector<int32_t>& idx, std::vector<TmpNode>& tmp) {
     idx.resize((size_t)s.n_tris);
@@ -592,6 +644,10 @@ static void build_sah_tree(HostScene& s, int n_threads, int max_leaf, std::vecto
     if (const char* e = std::getenv("PRT_SAH_BINS")) b.NB = std::max(2, std::min((int)SahBuilder::NB_MAX, std::atoi(e)));
     if (const char* e = std::getenv("PRT_SAH_SWEEP_BELOW")) b.sweep_below = std::max(0, std::atoi(e));
     b.build(0, 0, (int32_t)s.n_tris, par + 1);
+    if (const char* e = std::getenv("PRT_SAH_ROTATE")) {
+        const int applied = rotate_tree(tmp, std::max(0, std::atoi(e)));
+        if (std::getenv("PRT_DEBUG_BUILD")) std::fprintf(stderr, "[prt] tree rotations applied: %d\n", applied);
+    }
 }
 
 static void finish_slots(HostScene& s) {
