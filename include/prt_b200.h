@@ -11,8 +11,9 @@
  * This header is the boundary a maintainer would bind instead (INTEGRATION.md shows the stub):
  * plain pointers and sizes, no C++ / torch types, every call returns an int status (0 = ok) and
  * never throws. Inputs are copied at create time (the caller keeps ownership); outputs are
- * caller-allocated. One context is bound to one GPU and is used from one host thread at a time
- * (one process per GPU; multi-GPU = one context per rank, see prt_render_device).
+ * caller-allocated. One context is bound to one GPU and is used from one host thread at a time.
+ * Multi-GPU: one prt_multi handle for the whole box from one process (prt_multi_*), or one
+ * context per rank with the caller's own reduce (prt_render_device).
  *
  * There is NO CPU fallback: every compute entry point fails with PRT_ERR_NO_DEVICE when the
  * context has no usable sm_100 device.
