@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--check", type=int, default=0, help="compare the first N rays with the CPU oracle")
     ap.add_argument("--max-leaf", type=int, default=0)
+    ap.add_argument("--split", default="contiguous", choices=["contiguous", "blocks"],
+                    help="under torchrun: rank r traces the r-th contiguous range of the batch (SURVEY 8e) or every N-th block of 65536 rays (balances a camera batch whose top rows are sky)")
     ap.add_argument("--accel", default=os.environ.get("PRT_BENCH_ACCEL", "auto"), choices=["auto", "bvh2", "bvh4", "lbvh", "bvh4q"])
     a = ap.parse_args()
     import torch
@@ -43,7 +45,12 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n_all = 1 << a.rays
     lo_, hi_ = ray_range(n_all, rank, world) if world > 1 else (0, n_all)
-    n = hi_ - lo_
+    if world > 1 and a.split == "blocks":
+        B = 65536
+        mine = np.concatenate([np.arange(b, min(b + B, n_all)) for b in range(rank * B, n_all, world * B)])
+    else:
+        mine = np.arange(lo_, hi_)
+    n = len(mine)
     if a.mesh == "terrain":
         sc = scenes.terrain(1000, 500) if a.tris == 1 else scenes.terrain(2500, 2000)
     else:
@@ -69,7 +76,7 @@ def main():
         else:
             side = 1 << (a.rays // 2)
             o, d = scenes.camera_rays(sc.camera, side, n_all // side)
-        o, d = np.ascontiguousarray(o[lo_:hi_]), np.ascontiguousarray(d[lo_:hi_])
+        o, d = np.ascontiguousarray(o[mine]), np.ascontiguousarray(d[mine])
         do, dd = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
         tmin = torch.full((n,), 1e-4, dtype=torch.float64, device="cuda")
         tmax = torch.full((n,), float("inf"), dtype=torch.float64, device="cuda")
@@ -77,7 +84,7 @@ def main():
         t = torch.zeros(n, dtype=torch.float64, device="cuda")  # a miss leaves t / alpha / beta untouched
         al, be = torch.zeros_like(t), torch.zeros_like(t)
         hit = torch.empty(n, dtype=torch.uint8, device="cuda")
-        tmax_any = torch.from_numpy(np.ascontiguousarray((scenes.hash_uniform(n_all, 5, 1) * diag)[lo_:hi_])).cuda()
+        tmax_any = torch.from_numpy(np.ascontiguousarray((scenes.hash_uniform(n_all, 5, 1) * diag)[mine])).cuda()
         tmin_any = torch.full((n,), 1e-3, dtype=torch.float64, device="cuda")
         torch.cuda.synchronize()
         for query in ("closest", "any"):
@@ -116,7 +123,7 @@ def main():
                     # cache-oblivious demand (every node / triangle fetch counted as if it came from HBM) against the HBM peak:
                     # above 1 on coherent batches, where L1 / L2 serve the fetches; the limiter ncu names is in profiles/r2_limiters.json
                     "algorithmic_gb_s": alg / (ms * 1e-3) / 1e9, "hbm_peak_gb_s": peak * world,
-                    "algorithmic_demand_vs_hbm": alg / (ms * 1e-3) / 1e9 / (peak * world), "accel": a.accel, "node_bytes": st.node_bytes,
+                    "algorithmic_demand_vs_hbm": alg / (ms * 1e-3) / 1e9 / (peak * world), "accel": a.accel, "node_bytes": st.node_bytes, "split": a.split if world > 1 else None,
                     "hit_fraction": hits / n_tot,
                     "scene_create_s": t_create, "scene_commit_s": t_commit, "n_nodes": st.n_nodes, "build_ms": st.build_ms}
             if a.check and query == "closest" and kind == "random":
