@@ -116,7 +116,7 @@ struct prt_scene {
     DevBuf<PathRec> p_rec;
     DevBuf<PathL> p_lum;
     DevBuf<PrimaryHit> p_primary;
-    DevBuf<int32_t> p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qm3, p_qs;
+    DevBuf<int32_t> p_q0, p_q1, p_qm0, p_qm1, p_qm2, p_qm3, p_qm4, p_qs;
     DevBuf<BounceCtrl> p_ctrl;
     /* ray binning (launch.h): keys, reordered queues, histograms + cursors; also used by the ray queries */
     DevBuf<uint16_t> p_ke, p_ks;
@@ -201,6 +201,7 @@ int ensure_pool(prt_scene* s, int64_t cap, int64_t npix, int n_bounces, bool bin
         CUDA_TRY(s->p_qm1.ensure((size_t)cap));
         CUDA_TRY(s->p_qm2.ensure((size_t)cap));
         CUDA_TRY(s->p_qm3.ensure((size_t)cap));
+        CUDA_TRY(s->p_qm4.ensure((size_t)cap));
         CUDA_TRY(s->p_qs.ensure((size_t)cap));
         s->pool_cap = cap;
     }
@@ -218,7 +219,7 @@ PathBuffers path_buffers(prt_scene* s) {
     pb.lum = s->p_lum.p;
     pb.primary = s->p_primary.p;
     pb.q_extend[0] = s->p_q0.p; pb.q_extend[1] = s->p_q1.p;
-    pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p; pb.q_mat[3] = s->p_qm3.p;
+    pb.q_mat[0] = s->p_qm0.p; pb.q_mat[1] = s->p_qm1.p; pb.q_mat[2] = s->p_qm2.p; pb.q_mat[3] = s->p_qm3.p; pb.q_mat[4] = s->p_qm4.p;
     pb.q_shadow = s->p_qs.p;
     pb.ctrl = s->p_ctrl.p;
     pb.key_extend = s->p_ke.p; pb.key_shadow = s->p_ks.p;
@@ -455,7 +456,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
         uint8_t c;
         if (m.has_emission) c = CLS_EMISSIVE;
         else if (m.type == PRT_MAT_LAMBERTIAN) c = CLS_LAMBERT;
-        else if (m.type == PRT_MAT_PHONG) c = CLS_PHONG;
+        else if (m.type == PRT_MAT_PHONG) c = m.pks > 0.0 ? CLS_PHONG_SPEC : CLS_PHONG; /* launch.h: the specular lobe gets its own queue */
         else if (m.type == PRT_MAT_MIRROR) c = CLS_MIRROR;
         else if (m.type == PRT_MAT_COOK_TORRANCE) c = CLS_COOK;
         else if (m.type == PRT_MAT_EMPTY) c = CLS_EMPTY;

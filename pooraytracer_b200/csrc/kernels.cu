@@ -383,7 +383,7 @@ struct PrimaryPolicy {
         return true;
     }
     __device__ __forceinline__ void flush() {
-        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2], pb.q_mat[3]};
+        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2], pb.q_mat[3], pb.q_mat[4]};
         push.complete(queues);
     }
     __device__ __forceinline__ void retire(bool finished, int32_t pix, const Hit& h) {
@@ -400,7 +400,7 @@ struct PrimaryPolicy {
                 st256g(pb.primary + pix, le.x, le.y, le.z, pack2((uint32_t)prim, (uint32_t)c));
             }
         }
-        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2], &ctrl->n_mat[3]};
+        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2], &ctrl->n_mat[3], &ctrl->n_mat[4]};
         push.issue(counters, cls, pix);
         flush();
     }
@@ -447,7 +447,7 @@ struct ExtendPolicy {
         return true;
     }
     __device__ __forceinline__ void flush() {
-        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2], pb.q_mat[3]};
+        int32_t* const queues[CLS_SHADED] = {pb.q_mat[0], pb.q_mat[1], pb.q_mat[2], pb.q_mat[3], pb.q_mat[4]};
         push.complete(queues);
     }
     __device__ __forceinline__ void retire(bool finished, int32_t slot, const Hit& h) {
@@ -495,7 +495,7 @@ struct ExtendPolicy {
             }
             /* CLS_EMPTY past bounce 0: no NEE, Scatter returns false (Material.h:537-540): the path just ends */
         }
-        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2], &ctrl->n_mat[3]};
+        int32_t* const counters[CLS_SHADED] = {&ctrl->n_mat[0], &ctrl->n_mat[1], &ctrl->n_mat[2], &ctrl->n_mat[3], &ctrl->n_mat[4]};
         push.issue(counters, cls, slot);
 #if !PRT_EXTEND_DEFER
         flush();
@@ -600,7 +600,7 @@ __device__ __forceinline__ void shade_vertex(const DevScene& S, const RenderCons
             const d3 emission = mk3(lm->emission[0], lm->emission[1], lm->emission[2]);
             const d3 local_wi = world_to_local(light_dir, s);
             const d3 local_ln = world_to_local(ls.normal, s);
-            const d3 fr = material_eval(S, m, local_wi, wo, s.uv, rng);
+            const d3 fr = material_eval<CLS == CLS_COOK, CLS == CLS_PHONG || CLS == CLS_PHONG_SPEC, CLS == CLS_PHONG_SPEC>(S, m, local_wi, wo, s.uv, rng);
             const double cos_theta = local_wi.z;
             const double cos_theta_bar = dot(local_ln, -local_wi);
             d3 direct = emission * fr * cos_theta * cos_theta_bar / (distance * distance) / ls.pdf;
@@ -627,7 +627,8 @@ __device__ __forceinline__ void shade_vertex(const DevScene& S, const RenderCons
         bool scattered = true;
         double cosine_pdf = 0.0;
         if (CLS == CLS_LAMBERT) scatter_lambertian(S, m, s, rng, att, sd, cosine_pdf);
-        else if (CLS == CLS_PHONG) scatter_phong(S, m, s, wo, rng, att, sd, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
+        else if (CLS == CLS_PHONG) scatter_phong<false>(S, m, s, wo, rng, att, sd, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
+        else if (CLS == CLS_PHONG_SPEC) scatter_phong<true>(S, m, s, wo, rng, att, sd, cosine_pdf, (rc.flags & PRT_RENDER_LOBE_PROBABILITY) != 0);
         else if (CLS == CLS_COOK) scattered = scatter_cook(m, s, wo, rng, att, sd);
         else scatter_mirror(s, wo, att, sd);
         /* RayColor(depth - 1) of the last allowed vertex returns 0 (Camera.cpp:121) */
@@ -964,6 +965,7 @@ __global__ void __launch_bounds__(128, 2) k_tail(DevScene S, const uint8_t* __re
         if (rc.class_mask & (1 << CLS_PHONG)) shade_body<CLS_PHONG, false>(S, rc, pb, b, 0, sm_stack);
         if (rc.class_mask & (1 << CLS_MIRROR)) shade_body<CLS_MIRROR, false>(S, rc, pb, b, 0, sm_stack);
         if (rc.class_mask & (1 << CLS_COOK)) shade_body<CLS_COOK, false>(S, rc, pb, b, 0, sm_stack);
+        if (rc.class_mask & (1 << CLS_PHONG_SPEC)) shade_body<CLS_PHONG_SPEC, false>(S, rc, pb, b, 0, sm_stack);
         grid.sync();
         if (rc.sample_lights) {
             shadow_body<COUNT, WIDE>(S, rc, pb, b, 0, cnt, sm_stack);
@@ -1145,6 +1147,7 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
     const int g_shade1 = persistent_grid(k_shade<CLS_PHONG, false>, 128, shade_lc, rc.n_paths);
     const int g_shade2 = persistent_grid(k_shade<CLS_MIRROR, false>, 128, shade_lc, rc.n_paths);
     const int g_shade3 = persistent_grid(k_shade<CLS_COOK, false>, 128, shade_lc, rc.n_paths);
+    const int g_shade4 = persistent_grid(k_shade<CLS_PHONG_SPEC, false>, 128, shade_lc, rc.n_paths);
     cudaEvent_t* ev = lc.stage_events;
     /* Both per-bounce decisions are taken here from the EXPECTED queue length n_paths * rr^bounce
      * (Russian roulette thins the wavefront geometrically; the host never reads a queue length back):
@@ -1171,11 +1174,13 @@ int launch_render_pass(const DevScene& S, const uint8_t* prim_class, const Rende
             if (rc.class_mask & (1 << CLS_PHONG)) { k_shade<CLS_PHONG, true><<<persistent_grid(k_shade<CLS_PHONG, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
             if (rc.class_mask & (1 << CLS_MIRROR)) { k_shade<CLS_MIRROR, true><<<persistent_grid(k_shade<CLS_MIRROR, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
             if (rc.class_mask & (1 << CLS_COOK)) { k_shade<CLS_COOK, true><<<persistent_grid(k_shade<CLS_COOK, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_PHONG_SPEC)) { k_shade<CLS_PHONG_SPEC, true><<<persistent_grid(k_shade<CLS_PHONG_SPEC, true>, 128, shade_lc, rc.n_paths), 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
         } else {
             if (rc.class_mask & (1 << CLS_LAMBERT)) { k_shade<CLS_LAMBERT, false><<<g_shade0, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
             if (rc.class_mask & (1 << CLS_PHONG)) { k_shade<CLS_PHONG, false><<<g_shade1, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
             if (rc.class_mask & (1 << CLS_MIRROR)) { k_shade<CLS_MIRROR, false><<<g_shade2, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
             if (rc.class_mask & (1 << CLS_COOK)) { k_shade<CLS_COOK, false><<<g_shade3, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
+            if (rc.class_mask & (1 << CLS_PHONG_SPEC)) { k_shade<CLS_PHONG_SPEC, false><<<g_shade4, 128, 0, st>>>(S, rc, pb, b, sort); ++launches; }
         }
         if (sort) {
             BounceCtrl* dc = pb.ctrl + b;

@@ -156,15 +156,19 @@ __device__ __forceinline__ d3 reflect(d3 wo, d3 n) { return -wo + 2. * dot(wo, n
 /* ---- BSDFs ------------------------------------------------------------------------------------- */
 /* Material::Eval as the NEE estimator calls it (Camera.cpp:168); wi, wo in the local frame */
 __device__ __forceinline__ d3 cook_eval(const DevMaterial& m, d3 wi, d3 wo); /* cook_torrance.cuh */
+/* COOK / PHONG / PHONG_SPEC: which of the branches the calling kernel's material class can reach at all (launch.h: a class
+ * holds one material type; CLS_PHONG holds the Phong materials with pks == 0, whose specular branch is unreachable because
+ * u < pkd = 1 always). The other branches are compiled out: same arithmetic, a third of the code. */
+template <bool COOK = true, bool PHONG = true, bool PHONG_SPEC = true>
 __device__ __forceinline__ d3 material_eval(const DevScene& S, const DevMaterial& m, d3 wi, d3 wo, d2 uv, const Rng& rng) {
-    if (m.type == PRT_MAT_COOK_TORRANCE) return cook_eval(m, wi, wo);
+    if (COOK && m.type == PRT_MAT_COOK_TORRANCE) return cook_eval(m, wi, wo);
     if (m.type == PRT_MAT_LAMBERTIAN) return tex_or_color(S, m.kd_tex, m.kd, uv) * PRT_INV_PI;
-    if (m.type == PRT_MAT_PHONG) {
+    if (PHONG && m.type == PRT_MAT_PHONG) {
         const double u = rng.peek(); /* Material.h:228: the value is looked at, the stream position is not moved (header comment) */
         if (u < m.pkd) {
             if (wi.z <= 0) return mk3(0, 0, 0);
             return tex_or_color(S, m.kd_tex, m.kd, uv) * PRT_INV_PI;
-        } else if (m.pkd <= u && u < m.pkd + m.pks) {
+        } else if (PHONG_SPEC && m.pkd <= u && u < m.pkd + m.pks) {
             if (wi.z <= 0) return mk3(0, 0, 0);
             const d3 local_reflect = normalize(reflect(wo, mk3(0., 0., 1.)));
             const double ca = fmax(0., dot(wi, local_reflect));
@@ -188,7 +192,9 @@ __device__ __forceinline__ void scatter_lambertian(const DevScene& S, const DevM
     att = f * wi.z / pdf;
 }
 
-/* lobe_probability (PRT_RENDER_LOBE_PROBABILITY, never the parity default): divide by the probability of the sampled lobe */
+/* lobe_probability (PRT_RENDER_LOBE_PROBABILITY, never the parity default): divide by the probability of the sampled lobe.
+ * SPEC = false: the material has pks == 0 (CLS_PHONG), the specular branch cannot be taken and is compiled out. */
+template <bool SPEC = true>
 __device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMaterial& m, const Surface& s, d3 wo, Rng& rng, d3& att, d3& out_dir,
                                               double& cosine_pdf, bool lobe_probability = false) {
     d3 wi = mk3(0, 0, 0), f = mk3(0, 0, 0);
@@ -198,7 +204,7 @@ __device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMateri
         wi = sample_cosine_hemisphere_upper(rng);
         pdf = wi.z * PRT_INV_PI;
         f = tex_or_color(S, m.kd_tex, m.kd, s.uv) * PRT_INV_PI;
-    } else if (m.pkd <= u && u < m.pkd + m.pks) {
+    } else if (SPEC && m.pkd <= u && u < m.pkd + m.pks) {
         const double u1 = rng.next(), u2 = rng.next();
         const double alpha = acos(pow(u1, 1.0 / (m.ns + 1.0)));
         const double phi = 2.0 * PRT_PI * u2;
@@ -216,10 +222,16 @@ __device__ __forceinline__ void scatter_phong(const DevScene& S, const DevMateri
         const d3 T = normalize(cross(V, local_r));
         const d3 B = cross(local_r, T);
         wi = rw.x * T + rw.y * B + rw.z * local_r;
-        if (wi.z <= 0.) pdf = 0.0; /* SpecularPDF, Material.h:255-261 */
-        else pdf = (m.ns + 1.0) * PRT_INV_2PI * pow(dot(wi, local_r), m.ns);
-        const double lca = fmax(0.0, dot(wi, local_r));
-        if (wi.z > 0. && lca > 0.) f = tex_or_color(S, m.kd_tex, m.ks, s.uv) * (m.ns + 2.) * PRT_INV_2PI * pow(lca, m.ns);
+        /* SpecularPDF (Material.h:255-261) raises dot(wi, r) to Ns, Eval (Material.h:236-244) raises max(0, dot(wi, r)):
+         * where Eval's value is used at all (lca > 0) the two are the same number, so ONE pow serves both (it is ~300
+         * instructions, and the whole warp runs it for the one or two lanes in this branch) */
+        const double dl = dot(wi, local_r);
+        const double lca = fmax(0.0, dl);
+        double pw = 0.0;
+        if (wi.z > 0.) pw = pow(dl, m.ns);
+        if (wi.z <= 0.) pdf = 0.0;
+        else pdf = (m.ns + 1.0) * PRT_INV_2PI * pw;
+        if (wi.z > 0. && lca > 0.) f = tex_or_color(S, m.kd_tex, m.ks, s.uv) * (m.ns + 2.) * PRT_INV_2PI * pw;
     }
     out_dir = local_to_world(wi, s);
     att = mk3(0, 0, 0);
