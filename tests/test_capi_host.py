@@ -77,6 +77,24 @@ def test_compute_calls_fail_loudly_without_gpu(built):
     assert e.value.code == capi.PRT_ERR_NO_DEVICE
 
 
+def test_whole_box_handle_and_noalloc_entry_fail_loudly_without_gpu(built):
+    """prt_multi_create brings the other GPUs' contexts up on threads of its own: without a GPU every one of them must
+    fail into ONE clean error (no hang, no crash on the way out); the entry point without allocations refuses a host-only
+    scene like every other compute call."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is visible")
+    from pooraytracer_b200 import MultiScene
+    for devices in ([0], [0, 1], [0, 1, 2, 3, 4, 5, 6, 7]):
+        with pytest.raises(PrtError) as e:
+            MultiScene(devices, cases.tiny())
+        assert e.value.code == capi.PRT_ERR_NO_DEVICE
+    s = Scene(Context(-1), cases.tiny())
+    rc = s.lib.prt_trace_closest_device_noalloc(s.handle, 8, 1, 1, 1, 1, 1, None, None, None, None)
+    assert rc == capi.PRT_ERR_NO_DEVICE
+    assert s.lib.prt_multi_reduce_kind(None) == capi.REDUCE_NONE
+
+
 def test_bad_descriptions_are_rejected(built):
     sc = cases.tiny()
     bad = scenes.SceneData(name="bad", vertices=sc.vertices, texcoords=sc.texcoords, mesh_first=sc.mesh_first.copy(),
