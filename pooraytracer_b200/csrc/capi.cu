@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -140,6 +141,18 @@ struct prt_scene {
 };
 
 namespace {
+
+/* PRT_BUILD_TIMING=1: wall time of the host-side stages of scene creation / commit on stderr */
+struct HostStageTimer {
+    const bool on = std::getenv("PRT_BUILD_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void lap(const char* what) {
+        if (!on) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[prt] host %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t).count());
+        t = now;
+    }
+};
 
 int need_device(const prt_scene* s) {
     if (!s) return fail(PRT_ERR_INVALID_ARGUMENT, "null scene");
@@ -345,12 +358,15 @@ int prt_scene_create(prt_context* ctx, const prt_scene_desc* desc, prt_scene** o
     if (!s) return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_create: out of host memory");
     s->ctx = ctx;
     try {
+        HostStageTimer timer;
         if (!s->host.ingest(desc)) {
             std::string msg = s->host.error;
             delete s;
             return fail(PRT_ERR_INVALID_ARGUMENT, msg);
         }
+        timer.lap("ingest + triangle records");
         s->host.build_reference_bvhs(default_host_threads());
+        timer.lap("reference BVHs (DFS order)");
     } catch (const std::bad_alloc&) {
         delete s;
         return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_create: out of host memory");
@@ -384,6 +400,7 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
             if (p == 0 || b > scene_hi[k]) scene_hi[k] = b;
         }
     DeviceBvh dbvh;
+    HostStageTimer stage_timer;
     try {
         if (dev_build) {
             /* Morton sort, hierarchy, boxes, BVH4 emission and the triangle permutation
@@ -421,9 +438,11 @@ int prt_scene_commit(prt_scene* s, const prt_build_opts* opts) {
             s->d_tris.p = dbvh.tris; s->d_tris.n = (size_t)h.n_tris;
         } else if (accel == PRT_ACCEL_SAH_BVH2) h.build_sah_bvh2(default_host_threads(), max_leaf);
         else if (accel == PRT_ACCEL_SAH_BVH4) h.build_sah_bvh4(default_host_threads(), max_leaf);
-        else if (accel == PRT_ACCEL_SAH_BVH4Q) { h.build_sah_bvh4(default_host_threads(), max_leaf); h.quantise_bvh4(); }
+        else if (accel == PRT_ACCEL_SAH_BVH4Q) { h.build_sah_bvh4(default_host_threads(), max_leaf); stage_timer.lap("SAH tree + BVH4 + slots"); h.quantise_bvh4(); }
         else h.use_reference_slots();
+        stage_timer.lap("traversal tree");
         h.flatten_reference_world();
+        stage_timer.lap("reference tree flattened");
     } catch (const std::bad_alloc&) {
         return fail(PRT_ERR_OUT_OF_MEMORY, "prt_scene_commit: out of host memory");
     }

@@ -16,10 +16,14 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <limits>
+#include <memory>
 #include <thread>
 
 namespace prt {
@@ -114,6 +118,10 @@ void parallel_ranges(int64_t n, int n_threads, const std::function<void(int64_t,
 }  // namespace
 
 int default_host_threads() {
+    if (const char* e = std::getenv("PRT_HOST_THREADS")) { /* every host-side build gives the same result for any count */
+        const int v = std::atoi(e);
+        if (v >= 1) return v > 32 ? 32 : v;
+    }
     unsigned h = std::thread::hardware_concurrency();
     if (h == 0) h = 4;
     if (h > 32) h = 32;
@@ -293,14 +301,17 @@ struct RefBuilder {
     }
 };
 
-int32_t build_ref_tree(HostScene& s, std::vector<KeyRef>& items, int n_threads) {
-    const int64_t span = (int64_t)items.size();
-    const int32_t at = (int32_t)s.ref_nodes.size();
-    s.ref_nodes.resize(s.ref_nodes.size() + (size_t)ref_node_count(span));
+/* builds a tree over `items` into ref_nodes[at, at + ref_node_count(size)), which the caller has already made room for */
+void build_ref_tree_at(HostScene& s, std::vector<KeyRef>& items, int32_t at, int n_threads) {
     int par = 0;
     while ((1 << par) < n_threads) ++par;
     RefBuilder b(s, items);
-    b.build(0, span, at, par + 1);
+    b.build(0, (int64_t)items.size(), at, par + 1);
+}
+int32_t build_ref_tree(HostScene& s, std::vector<KeyRef>& items, int n_threads) {
+    const int32_t at = (int32_t)s.ref_nodes.size();
+    s.ref_nodes.resize(s.ref_nodes.size() + (size_t)ref_node_count((int64_t)items.size()));
+    build_ref_tree_at(s, items, at, n_threads);
     return at;
 }
 
@@ -324,15 +335,52 @@ void HostScene::build_reference_bvhs(int n_threads) {
     world_root = lights_root = -1;
     std::vector<ObjRef> world, lights;
     const int n_meshes = (int)mesh_material.size();
-    for (int m = 0; m < n_meshes; ++m) { /* main.cpp:37-43 */
+    /* one tree per mesh (main.cpp:37-43), a second one for an emissive mesh. The trees are independent, so they are built
+     * side by side on the host threads; every tree's place in ref_nodes is fixed beforehand, in mesh order, so the
+     * node numbering does not depend on which thread finishes first */
+    struct MeshJob { int m; int32_t at_world, at_light; };
+    std::vector<MeshJob> jobs;
+    size_t total = 0;
+    for (int m = 0; m < n_meshes; ++m) {
         if (mesh_first[m + 1] <= mesh_first[m]) continue;
-        std::vector<KeyRef> items;
-        items.reserve((size_t)(mesh_first[m + 1] - mesh_first[m]));
-        for (int64_t f = mesh_first[m]; f < mesh_first[m + 1]; ++f) items.push_back(KeyRef{0.0, ObjRef{0, (int32_t)f}});
-        /* BVHNode(shared_ptr<Mesh>) sorts mesh->objects IN PLACE (BVH.cpp:49): the second build
-         * for an emissive mesh starts from the order the first one left behind */
-        world.push_back(ObjRef{1, build_ref_tree(*this, items, n_threads)});
-        if (dev_materials[mesh_material[m]].has_emission) lights.push_back(ObjRef{1, build_ref_tree(*this, items, n_threads)});
+        const int64_t cnt = ref_node_count(mesh_first[m + 1] - mesh_first[m]);
+        MeshJob j{m, (int32_t)total, -1};
+        total += (size_t)cnt;
+        if (dev_materials[mesh_material[m]].has_emission) { j.at_light = (int32_t)total; total += (size_t)cnt; }
+        jobs.push_back(j);
+    }
+    ref_nodes.resize(total);
+    {
+        std::vector<size_t> by_size(jobs.size());
+        for (size_t i = 0; i < jobs.size(); ++i) by_size[i] = i;
+        std::sort(by_size.begin(), by_size.end(), [&](size_t a, size_t b) { /* largest first: the long jobs start early */
+            const int64_t sa = mesh_first[jobs[a].m + 1] - mesh_first[jobs[a].m], sb = mesh_first[jobs[b].m + 1] - mesh_first[jobs[b].m];
+            return sa != sb ? sa > sb : a < b;
+        });
+        std::atomic<size_t> next_job{0};
+        auto worker = [&]() {
+            for (;;) {
+                const size_t k = next_job.fetch_add(1);
+                if (k >= jobs.size()) return;
+                const MeshJob& j = jobs[by_size[k]];
+                std::vector<KeyRef> items;
+                items.reserve((size_t)(mesh_first[j.m + 1] - mesh_first[j.m]));
+                for (int64_t f = mesh_first[j.m]; f < mesh_first[j.m + 1]; ++f) items.push_back(KeyRef{0.0, ObjRef{0, (int32_t)f}});
+                /* BVHNode(shared_ptr<Mesh>) sorts mesh->objects IN PLACE (BVH.cpp:49): the second build
+                 * for an emissive mesh starts from the order the first one left behind */
+                build_ref_tree_at(*this, items, j.at_world, n_threads);
+                if (j.at_light >= 0) build_ref_tree_at(*this, items, j.at_light, n_threads);
+            }
+        };
+        const int n_workers = (int)std::min<size_t>((size_t)std::max(1, n_threads), jobs.size());
+        std::vector<std::thread> pool;
+        for (int t = 1; t < n_workers; ++t) pool.emplace_back(worker);
+        worker();
+        for (auto& t : pool) t.join();
+    }
+    for (const MeshJob& j : jobs) {
+        world.push_back(ObjRef{1, j.at_world});
+        if (j.at_light >= 0) lights.push_back(ObjRef{1, j.at_light});
     }
     auto top = [&](std::vector<ObjRef>& list) -> int32_t { /* main.cpp:44-45 */
         if (list.empty()) return -1;
@@ -439,29 +487,45 @@ struct TmpNode {
     int32_t first = 0, count = 0;  /* leaf: range in the index array */
 };
 
+/* what the builder permutes: a triangle's box travels with its index, so that every pass over a node's triangles is a
+ * sequential read (an index array alone made each pass a gather from the box array: one cache miss per triangle and level) */
+struct BoxRef {
+    Box6 box;
+    int32_t prim;
+};
+
 struct SahBuilder {
     const HostScene& s;
-    std::vector<int32_t>& idx;
+    std::vector<BoxRef>& work;
     std::vector<TmpNode>& nodes;
     std::atomic<int32_t>& next;
     int max_leaf;
     static constexpr int NB_MAX = 64;
+    static constexpr int32_t PAR_BINS = 131072; /* nodes of at least this many triangles bin on several host threads */
+    int n_threads = 1;
     int NB = 16;           /* bins per axis, at most NB_MAX (build_sah_tree picks; PRT_SAH_BINS overrides) */
     int sweep_below = 0;   /* PRT_SAH_SWEEP_BELOW (experiments): subtrees of fewer triangles try EVERY split position */
     double C_TRI = 1.25, C_NODE = 1.0; /* PRT_SAH_CTRI overrides C_TRI (experiments) */
 
     int32_t alloc() { return next.fetch_add(1); }
 
-    void build(int32_t at, int32_t first, int32_t count, int par_depth) {
+    /* pre_box / pre_cbox: the node's box and the box of its centroids where the parent already knows them (the unions of
+     * the bins on either side of its split: min / max are exact, so they are the very values the pass below would find) */
+    void build(int32_t at, int32_t first, int32_t count, int par_depth, const Box6* pre_box = nullptr, const Box6* pre_cbox = nullptr) {
         TmpNode& N = nodes[at];
         Box6 box = box_empty(), cbox = box_empty();
-        for (int32_t i = first; i < first + count; ++i) {
-            const Box6& b = s.tri_box[idx[i]];
-            box_grow(box, b);
-            for (int k = 0; k < 3; ++k) {
-                const double c = 0.5 * (b.v[2 * k] + b.v[2 * k + 1]);
-                if (c < cbox.v[2 * k]) cbox.v[2 * k] = c;
-                if (c > cbox.v[2 * k + 1]) cbox.v[2 * k + 1] = c;
+        if (pre_box && pre_cbox) {
+            box = *pre_box;
+            cbox = *pre_cbox;
+        } else {
+            for (int32_t i = first; i < first + count; ++i) {
+                const Box6& b = work[i].box;
+                box_grow(box, b);
+                for (int k = 0; k < 3; ++k) {
+                    const double c = 0.5 * (b.v[2 * k] + b.v[2 * k + 1]);
+                    if (c < cbox.v[2 * k]) cbox.v[2 * k] = c;
+                    if (c > cbox.v[2 * k + 1]) cbox.v[2 * k + 1] = c;
+                }
             }
         }
         N.box = box;
@@ -473,9 +537,12 @@ struct SahBuilder {
         double best_cost = std::numeric_limits<double>::infinity();
         const double parent_area = half_area(box);
         int32_t sweep_mid = -1; /* >= 0: idx[first, first + count) is already ordered for the best sweep split */
+        Box6 child_box[2], child_cbox[2];
+        bool child_known = false;
         if (count < sweep_below) {
             /* full sweep: order by centroid on each axis, every one of the count - 1 split positions is a candidate */
-            std::vector<int32_t> order(idx.begin() + first, idx.begin() + first + count), best_order;
+            std::vector<int32_t> order((size_t)count), best_order;
+            for (int32_t i = 0; i < count; ++i) order[i] = work[first + i].prim;
             std::vector<double> right((size_t)count);
             for (int axis = 0; axis < 3; ++axis) {
                 std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
@@ -492,42 +559,155 @@ struct SahBuilder {
                 }
                 if (best_axis == axis) best_order = order;
             }
-            if (sweep_mid >= 0) std::copy(best_order.begin(), best_order.end(), idx.begin() + first);
-        } else
-        for (int axis = 0; axis < 3; ++axis) {
-            const double lo = cbox.v[2 * axis], ext = cbox.v[2 * axis + 1] - lo;
-            if (!(ext > 0.0)) continue;
-            int cnt[NB_MAX];
-            Box6 bb[NB_MAX];
-            for (int b = 0; b < NB; ++b) { cnt[b] = 0; bb[b] = box_empty(); }
-            const double scale = NB / ext;
-            for (int32_t i = first; i < first + count; ++i) {
-                const Box6& b = s.tri_box[idx[i]];
-                const double c = 0.5 * (b.v[2 * axis] + b.v[2 * axis + 1]);
-                int bin = (int)((c - lo) * scale);
-                if (bin < 0) bin = 0;
-                if (bin >= NB) bin = NB - 1;
-                cnt[bin]++;
-                box_grow(bb[bin], b);
+            if (sweep_mid >= 0)
+                for (int32_t i = 0; i < count; ++i) work[first + i] = BoxRef{s.tri_box[best_order[i]], best_order[i]};
+        } else {
+            /* ONE pass over the triangles fills the bins of all three axes (tri_box[idx[i]] is a random access: three
+             * passes were three cache misses per triangle and level); above PAR_BINS triangles the pass is cut into
+             * ranges for the host threads, whose bins are merged in range order — counts add, boxes take min / max, so
+             * the merged bins, and with them the tree, do not depend on the number of threads */
+            double lo3[3], scale3[3];
+            bool use[3];
+            for (int axis = 0; axis < 3; ++axis) {
+                lo3[axis] = cbox.v[2 * axis];
+                const double ext = cbox.v[2 * axis + 1] - lo3[axis];
+                use[axis] = ext > 0.0;
+                scale3[axis] = use[axis] ? NB / ext : 0.0;
             }
-            double right_area[NB_MAX];
-            int right_cnt[NB_MAX];
-            Box6 acc = box_empty();
-            int c = 0;
-            for (int b = NB - 1; b > 0; --b) {
-                box_grow(acc, bb[b]);
-                c += cnt[b];
-                right_area[b] = c ? half_area(acc) : 0.0;
-                right_cnt[b] = c;
+            struct Bins {
+                int cnt[3][NB_MAX];
+                Box6 bb[3][NB_MAX]; /* union of the triangle boxes of the bin */
+                Box6 cb[3][NB_MAX]; /* box of their centroids */
+            };
+            /* only the counts are cleared (768 bytes): a bin's boxes are initialised when its first triangle arrives, and
+             * the scans below skip empty bins. Most nodes of a tree hold a handful of triangles; clearing and scanning
+             * 3 x 64 boxes for each of them was most of the build time (5.5 GB of stores for 1.1 M triangles). */
+            auto clear_bins = [&](Bins& B) {
+                for (int axis = 0; axis < 3; ++axis)
+                    for (int b = 0; b < NB; ++b) B.cnt[axis][b] = 0;
+            };
+            auto fill_bins = [&](int32_t from, int32_t to, Bins& B) {
+                for (int32_t i = from; i < to; ++i) {
+                    const Box6& b = work[i].box;
+                    const double c3[3] = {0.5 * (b.v[0] + b.v[1]), 0.5 * (b.v[2] + b.v[3]), 0.5 * (b.v[4] + b.v[5])};
+                    for (int axis = 0; axis < 3; ++axis) {
+                        if (!use[axis]) continue;
+                        int bin = (int)((c3[axis] - lo3[axis]) * scale3[axis]);
+                        if (bin < 0) bin = 0;
+                        if (bin >= NB) bin = NB - 1;
+                        if (B.cnt[axis][bin]++ == 0) { B.bb[axis][bin] = box_empty(); B.cb[axis][bin] = box_empty(); }
+                        box_grow(B.bb[axis][bin], b);
+                        Box6& cbn = B.cb[axis][bin];
+                        for (int k = 0; k < 3; ++k) {
+                            if (c3[k] < cbn.v[2 * k]) cbn.v[2 * k] = c3[k];
+                            if (c3[k] > cbn.v[2 * k + 1]) cbn.v[2 * k + 1] = c3[k];
+                        }
+                    }
+                }
+            };
+            static thread_local Bins tl_bins; /* done with before this call recurses */
+            static thread_local bool tl_clean = false; /* every count of tl_bins is zero */
+            Bins* const bins = &tl_bins;
+            if (!tl_clean) { clear_bins(*bins); tl_clean = true; }
+            /* non-empty bins per axis, ascending. A node of a few triangles (most nodes) keeps the list as it bins and
+             * touches nothing else: no clearing and no scan of 3 x 64 bins for a handful of triangles */
+            constexpr int SPARSE_MAX = 16;
+            const bool sparse = count <= SPARSE_MAX;
+            int ids[3][NB_MAX], n_ids[3] = {0, 0, 0};
+            const int helpers = count >= PAR_BINS ? std::min(n_threads, 16) : 1;
+            if (helpers > 1 && std::getenv("PRT_DEBUG_BUILD")) std::fprintf(stderr, "[prt] big node: %d triangles\n", count);
+            if (sparse) {
+                for (int32_t i = first; i < first + count; ++i) {
+                    const Box6& bx = work[i].box;
+                    const double c3[3] = {0.5 * (bx.v[0] + bx.v[1]), 0.5 * (bx.v[2] + bx.v[3]), 0.5 * (bx.v[4] + bx.v[5])};
+                    for (int axis = 0; axis < 3; ++axis) {
+                        if (!use[axis]) continue;
+                        int bin = (int)((c3[axis] - lo3[axis]) * scale3[axis]);
+                        if (bin < 0) bin = 0;
+                        if (bin >= NB) bin = NB - 1;
+                        if (bins->cnt[axis][bin]++ == 0) {
+                            bins->bb[axis][bin] = box_empty();
+                            bins->cb[axis][bin] = box_empty();
+                            int at_ = n_ids[axis]++;
+                            while (at_ > 0 && ids[axis][at_ - 1] > bin) { ids[axis][at_] = ids[axis][at_ - 1]; --at_; }
+                            ids[axis][at_] = bin;
+                        }
+                        box_grow(bins->bb[axis][bin], bx);
+                        Box6& cbn = bins->cb[axis][bin];
+                        for (int k = 0; k < 3; ++k) {
+                            if (c3[k] < cbn.v[2 * k]) cbn.v[2 * k] = c3[k];
+                            if (c3[k] > cbn.v[2 * k + 1]) cbn.v[2 * k + 1] = c3[k];
+                        }
+                    }
+                }
+            } else if (helpers > 1) {
+                std::vector<std::unique_ptr<Bins>> part((size_t)helpers);
+                std::vector<std::thread> th;
+                for (int t = 0; t < helpers; ++t) {
+                    part[t].reset(new Bins);
+                    clear_bins(*part[t]);
+                    const int32_t from = first + (int32_t)((int64_t)count * t / helpers), to = first + (int32_t)((int64_t)count * (t + 1) / helpers);
+                    th.emplace_back([&, t, from, to] { fill_bins(from, to, *part[t]); });
+                }
+                for (auto& t : th) t.join();
+                for (int t = 0; t < helpers; ++t)
+                    for (int axis = 0; axis < 3; ++axis)
+                        for (int b = 0; b < NB; ++b) {
+                            if (part[t]->cnt[axis][b] == 0) continue;
+                            if (bins->cnt[axis][b] == 0) { bins->bb[axis][b] = box_empty(); bins->cb[axis][b] = box_empty(); }
+                            bins->cnt[axis][b] += part[t]->cnt[axis][b];
+                            box_grow(bins->bb[axis][b], part[t]->bb[axis][b]);
+                            box_grow(bins->cb[axis][b], part[t]->cb[axis][b]);
+                        }
+            } else {
+                fill_bins(first, first + count, *bins);
             }
-            acc = box_empty();
-            c = 0;
-            for (int b = 0; b < NB - 1; ++b) {
-                box_grow(acc, bb[b]);
-                c += cnt[b];
-                if (c == 0 || right_cnt[b + 1] == 0) continue;
-                const double cost = half_area(acc) * c + right_area[b + 1] * right_cnt[b + 1];
-                if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = b; }
+            if (!sparse)
+                for (int axis = 0; axis < 3; ++axis)
+                    for (int b = 0; b < NB; ++b)
+                        if (use[axis] && bins->cnt[axis][b]) ids[axis][n_ids[axis]++] = b;
+            /* candidates: a split after every non-empty bin but the last. (Between two non-empty bins the split is the same
+             * two sets at the same cost; the strict comparison keeps the first, which is the one after the non-empty bin.) */
+            for (int axis = 0; axis < 3; ++axis) {
+                if (!use[axis]) continue;
+                const int* cnt = bins->cnt[axis];
+                const Box6* bb = bins->bb[axis];
+                const int m = n_ids[axis];
+                double right_area[NB_MAX];
+                int right_cnt[NB_MAX];
+                Box6 acc = box_empty();
+                int c = 0;
+                for (int j = m - 1; j > 0; --j) {
+                    box_grow(acc, bb[ids[axis][j]]);
+                    c += cnt[ids[axis][j]];
+                    right_area[j] = half_area(acc);
+                    right_cnt[j] = c;
+                }
+                acc = box_empty();
+                c = 0;
+                for (int j = 0; j + 1 < m; ++j) {
+                    const int bnow = ids[axis][j];
+                    box_grow(acc, bb[bnow]);
+                    c += cnt[bnow];
+                    const double cost = half_area(acc) * c + right_area[j + 1] * right_cnt[j + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = bnow; }
+                }
+            }
+            if (best_axis >= 0) { /* what the two children will hold, known without another pass over them */
+                for (int side = 0; side < 2; ++side) { child_box[side] = box_empty(); child_cbox[side] = box_empty(); }
+                for (int j = 0; j < n_ids[best_axis]; ++j) {
+                    const int bnow = ids[best_axis][j];
+                    const int side = bnow <= best_bin ? 0 : 1;
+                    box_grow(child_box[side], bins->bb[best_axis][bnow]);
+                    box_grow(child_cbox[side], bins->cb[best_axis][bnow]);
+                }
+                child_known = true;
+            }
+            if (sparse) { /* leave the counts as they were found: zero */
+                for (int axis = 0; axis < 3; ++axis)
+                    for (int j = 0; j < n_ids[axis]; ++j) bins->cnt[axis][ids[axis][j]] = 0;
+            } else {
+                tl_clean = false;
             }
         }
         if (count <= max_leaf) {
@@ -543,29 +723,34 @@ struct SahBuilder {
         } else if (best_axis >= 0) {
             const double lo = cbox.v[2 * best_axis], ext = cbox.v[2 * best_axis + 1] - lo;
             const double scale = NB / ext;
-            auto it = std::partition(idx.begin() + first, idx.begin() + first + count, [&](int32_t p) {
-                const Box6& b = s.tri_box[p];
+            auto it = std::partition(work.begin() + first, work.begin() + first + count, [&](const BoxRef& p) {
+                const Box6& b = p.box;
                 const double c = 0.5 * (b.v[2 * best_axis] + b.v[2 * best_axis + 1]);
                 int bin = (int)((c - lo) * scale);
                 if (bin < 0) bin = 0;
                 if (bin >= NB) bin = NB - 1;
                 return bin <= best_bin;
             });
-            mid = (int32_t)(it - idx.begin());
+            mid = (int32_t)(it - work.begin());
         } else {
             mid = first + count / 2; /* coincident centroids: split by position */
         }
-        if (mid == first || mid == first + count) mid = first + count / 2;
+        if (mid == first || mid == first + count) { mid = first + count / 2; child_known = false; }
         const int32_t l = alloc(), r = alloc();
         nodes[at].left = l;
         nodes[at].right = r;
-        if (par_depth > 0 && count > 65536) {
-            std::thread t([&, l]() { build(l, first, mid - first, par_depth - 1); });
-            build(r, mid, first + count - mid, par_depth - 1);
+        const Box6 *lb = child_known ? &child_box[0] : nullptr, *lc = child_known ? &child_cbox[0] : nullptr;
+        const Box6 *rb = child_known ? &child_box[1] : nullptr, *rcb = child_known ? &child_cbox[1] : nullptr;
+        const int32_t nl = mid - first, nr = first + count - mid;
+        /* a thread per split only where BOTH sides are worth one: SAH peels small pieces off a large rest (walls off a
+         * room), and a level of the thread budget spent on a 12-triangle side is a level the large rest does not get */
+        if (par_depth > 0 && std::min(nl, nr) > 32768) {
+            std::thread t([&, l]() { build(l, first, nl, par_depth - 1, lb, lc); });
+            build(r, mid, nr, par_depth - 1, rb, rcb);
             t.join();
         } else {
-            build(l, first, mid - first, 0);
-            build(r, mid, first + count - mid, 0);
+            build(l, first, nl, nl > 65536 ? par_depth : 0, lb, lc);
+            build(r, mid, nr, nr > 65536 ? par_depth : 0, rb, rcb);
         }
     }
 };
@@ -630,13 +815,14 @@ static int rotate_tree(std::vector<TmpNode>& t, int passes) {
 
 /* binned-SAH binary tree over all triangles (TmpNode[0] = root) + the permuted index array */
 static void build_sah_tree(HostScene& s, int n_threads, int max_leaf, std::vector<int32_t>& idx, std::vector<TmpNode>& tmp) {
-    idx.resize((size_t)s.n_tris);
-    for (int64_t i = 0; i < s.n_tris; ++i) idx[i] = (int32_t)i;
+    std::vector<BoxRef> work((size_t)s.n_tris);
+    for (int64_t i = 0; i < s.n_tris; ++i) work[i] = BoxRef{s.tri_box[i], (int32_t)i};
     tmp.assign((size_t)(2 * s.n_tris + 1), TmpNode());
     std::atomic<int32_t> next{1};
     int par = 0;
     while ((1 << par) < n_threads) ++par;
-    SahBuilder b{s, idx, tmp, next, max_leaf};
+    SahBuilder b{s, work, tmp, next, max_leaf};
+    b.n_threads = n_threads;
     /* 64 bins per axis on large meshes: -1.2 % nodes per ray and +2 % spp/s on the 1.1 M-triangle room for 0.1 s more build
      * time; no effect on the small scenes, whose trees stay as they were (profiles/r2_s19_builder_ab.txt) */
     b.NB = s.n_tris >= 262144 ? 64 : 16;
@@ -644,16 +830,37 @@ static void build_sah_tree(HostScene& s, int n_threads, int max_leaf, std::vecto
     if (const char* e = std::getenv("PRT_SAH_BINS")) b.NB = std::max(2, std::min((int)SahBuilder::NB_MAX, std::atoi(e)));
     if (const char* e = std::getenv("PRT_SAH_SWEEP_BELOW")) b.sweep_below = std::max(0, std::atoi(e));
     b.build(0, 0, (int32_t)s.n_tris, par + 1);
+    idx.resize((size_t)s.n_tris);
+    for (int64_t i = 0; i < s.n_tris; ++i) idx[i] = work[i].prim;
     if (const char* e = std::getenv("PRT_SAH_ROTATE")) {
         const int applied = rotate_tree(tmp, std::max(0, std::atoi(e)));
         if (std::getenv("PRT_DEBUG_BUILD")) std::fprintf(stderr, "[prt] tree rotations applied: %d\n", applied);
     }
 }
 
+/* PRT_DEBUG_BUILD=1: FNV-1a of the emitted nodes and of the slot order on stderr (two builds made the same tree iff equal) */
+static void debug_tree_checksum(const HostScene& s) {
+    if (!std::getenv("PRT_DEBUG_BUILD")) return;
+    auto fnv = [](const void* p, size_t n) {
+        uint64_t h = 1469598103934665603ull;
+        const unsigned char* b = (const unsigned char*)p;
+        for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; }
+        return h;
+    };
+    std::fprintf(stderr, "[prt] tree checksum: nodes2 %016llx nodes4 %016llx slots %016llx (%zu / %zu nodes)\n",
+                 (unsigned long long)fnv(s.nodes2.data(), s.nodes2.size() * sizeof(Node2)), (unsigned long long)fnv(s.nodes4.data(), s.nodes4.size() * sizeof(Node4)),
+                 (unsigned long long)fnv(s.slot_prim.data(), s.slot_prim.size() * sizeof(int32_t)), s.nodes2.size(), s.nodes4.size());
+}
+
 static void finish_slots(HostScene& s) {
-    for (size_t sidx = 0; sidx < s.slot_prim.size(); ++sidx) s.prim_slot[s.slot_prim[sidx]] = (int32_t)sidx;
+    debug_tree_checksum(s);
     s.isect_slots.resize((size_t)s.n_tris);
-    for (int64_t sidx = 0; sidx < s.n_tris; ++sidx) s.isect_slots[sidx] = s.isect[s.slot_prim[sidx]];
+    parallel_ranges(s.n_tris, default_host_threads(), [&](int64_t b, int64_t e) { /* a permutation: every entry written once */
+        for (int64_t sidx = b; sidx < e; ++sidx) {
+            s.prim_slot[s.slot_prim[sidx]] = (int32_t)sidx;
+            s.isect_slots[sidx] = s.isect[s.slot_prim[sidx]];
+        }
+    });
 }
 
 void HostScene::build_sah_bvh2(int n_threads, int max_leaf) {
@@ -733,7 +940,16 @@ void HostScene::build_sah_bvh4(int n_threads, int max_leaf) {
     if (n_tris == 0) return;
     std::vector<int32_t> idx;
     std::vector<TmpNode> tmp;
+    const bool timing = std::getenv("PRT_BUILD_TIMING") != nullptr;
+    auto t_lap = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[prt] host   %-26s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_lap).count());
+        t_lap = now;
+    };
     build_sah_tree(*this, n_threads, max_leaf, idx, tmp);
+    lap("binned SAH binary tree");
 
     slot_prim.reserve((size_t)n_tris);
     auto leaf_ref = [&](const TmpNode& n) -> int32_t {
@@ -797,7 +1013,9 @@ void HostScene::build_sah_bvh4(int n_threads, int max_leaf) {
         for (int i = nk - 1; i >= 0; --i)
             if (refs[i] >= 0) stack.push_back({kids[i], refs[i]});
     }
+    lap("collapse to BVH4 + emit");
     finish_slots(*this);
+    lap("slot tables + triangle gather");
 }
 
 /* Node4 -> Node4Q. Per node and axis: origin = the smallest child low (already an outward-rounded
@@ -806,7 +1024,8 @@ void HostScene::build_sah_bvh4(int n_threads, int max_leaf) {
  * one more step outward if rounding got in the way. */
 void HostScene::quantise_bvh4() {
     nodes4q.assign(nodes4.size(), Node4Q());
-    for (size_t n = 0; n < nodes4.size(); ++n) {
+    parallel_ranges((int64_t)nodes4.size(), default_host_threads(), [&](int64_t n_begin, int64_t n_end) { /* node by node, independent */
+    for (int64_t n = n_begin; n < n_end; ++n) {
         const Node4& N = nodes4[n];
         Node4Q Q;
         std::memset(&Q, 0, sizeof(Q));
@@ -859,6 +1078,13 @@ void HostScene::quantise_bvh4() {
             }
         }
         nodes4q[n] = Q;
+    }
+    });
+    if (std::getenv("PRT_DEBUG_BUILD")) {
+        uint64_t h = 1469598103934665603ull;
+        const unsigned char* b = (const unsigned char*)nodes4q.data();
+        for (size_t i = 0; i < nodes4q.size() * sizeof(Node4Q); ++i) { h ^= b[i]; h *= 1099511628211ull; }
+        std::fprintf(stderr, "[prt] tree checksum: nodes4q %016llx\n", (unsigned long long)h);
     }
 }
 
