@@ -163,6 +163,26 @@ def test_config2_and_3_full_frame_slice_vs_reference_render(gpu_ctx, built, name
     print(f"{name} slice: {frac:.5f} within 1e-9, rmse {rmse:.3e}; {sc.n_triangles} triangles, node bytes {st.node_bytes}")
 
 
+@pytest.mark.parametrize("kind", ["mixed", "cook"])
+def test_every_material_class_at_a_million_paths_vs_reference_render(gpu_ctx, built, kind):
+    """The unit-test scene (textured Lambert, Phong without and WITH a specular lobe — two shade classes —, mirror,
+    Empty, two lights; kind "cook": three CookTorrance materials, Material.h:368-521) at 512x512, 4 spp, depth 10:
+    1 M paths, so every shade class runs with queues many refills long, per-bounce launches and the tail kernel
+    both, against the CPU reference on the same streams."""
+    sc = scenes.tiny_scene(kind)
+    cam = make_camera(sc.camera, 512, 512)
+    prm = make_params(4, 10, rr=0.8, rng_key=KEY + 9)
+    O = ol.OracleScene(cpu_kind(), sc, ol.DEFINE_UB)
+    ref, info = O.render(cam, prm, ol.RNG_COUNTER, nthreads=CORES)
+    O.close()
+    assert info.paths == 4 * 512 * 512
+    for accel in (capi.ACCEL_SAH_BVH4, capi.ACCEL_SAH_BVH4Q):
+        s = Scene(gpu_ctx, sc, accel=accel)
+        frac, rmse = compare_same_streams(s.render(cam, prm), ref, f"tiny-{kind} 512x512 accel {accel}")
+        assert s.stats().ref_stack_overflows == 0
+    print(f"tiny-{kind} 512x512 spp 4 depth 10: {frac:.5f} within 1e-9, rmse {rmse:.3e}")
+
+
 def block_means(img, b=16):
     h, w, c = img.shape
     return img.reshape(h // b, b, w // b, b, c).mean(axis=(1, 3))
